@@ -1,0 +1,130 @@
+/* rf_b200.h -- C ABI of librf_b200.so, the B200-native field-synthesis path.
+ *
+ * The reference (dkirkby/randomfield) is pure Python and has no FFI of its own; its
+ * de-facto operator interface for this path is the set of in-place array functions that
+ * Generator.generate_delta_field calls (randomfield/generate.py:191-219) plus
+ * transform.Plan (randomfield/transform.py:161-315).  Each entry point below names the
+ * reference interface it replaces.  All functions return 0 on success and a negative
+ * status otherwise; rf_last_error() returns a human-readable message for the calling
+ * thread.  Plain pointers and sizes only -- no C++ or torch types.
+ *
+ * A context owns the device buffers of one Generator (one rank of a slab-decomposed grid).
+ * Calls on one context must be serialised by the caller; work is asynchronous on the
+ * context's CUDA stream until rf_sync / a host copy.
+ */
+#ifndef RF_B200_H
+#define RF_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rf_ctx rf_ctx;
+
+enum { RF_F32 = 0, RF_F64 = 1 };
+enum { RF_OK = 0, RF_ERR_ARG = -1, RF_ERR_CUDA = -2, RF_ERR_STATE = -3 };
+
+/* which device buffer rf_device_ptr returns */
+enum { RF_BUF_FIELD = 0, RF_BUF_RECV = 1, RF_BUF_PARTIALS = 2 };
+
+const char* rf_last_error(void);
+int rf_version(void);
+
+/* transform.Plan.__init__ / Generator.__init__ buffer allocation (transform.py:170-244,
+ * generate.py:76-80).  Grid (nx, ny, nz), all even.  rank/world describe the slab
+ * decomposition: this rank generates the k-space y-slab [rank*ny/world, (rank+1)*ny/world)
+ * and ends with the real-space x-slab [rank*nx/world, ...).  world == 1 for a single GPU. */
+int rf_create(int nx, int ny, int nz, int dtype, int rank, int world, rf_ctx** out);
+int rf_destroy(rf_ctx* ctx);
+
+/* run on an externally owned CUDA stream (cudaStream_t passed as void*); NULL restores
+ * the context's own stream */
+int rf_set_stream(rf_ctx* ctx, void* cuda_stream);
+int rf_sync(rf_ctx* ctx);
+
+/* powertools.tabulate_sigmas table (powertools.py:152-157): n knots, k[] strictly
+ * increasing and > 0, sigma[] = N3*sqrt(Pk/(2*Vbox)) in the reference normalisation
+ * (smoothing from powertools.filter_power already applied by the caller). */
+int rf_set_power(rf_ctx* ctx, int n, const double* k, const double* sigma, double spacing);
+
+/* White-noise injection (replaces the RandomState(seed).normal draw of random.py:24-28):
+ * host array of 2*nx*ny*(nz/2+1) doubles in the reference order, uploaded once.
+ * NULL clears it and returns to the Philox generator. */
+int rf_set_noise(rf_ctx* ctx, const double* host_noise);
+
+/* Pass 1 of generate_delta_field: fill_with_log10k + tabulate_sigmas + randomize +
+ * symmetrize (generate.py:191-199) fused with the axis-0 pass of Plan.execute
+ * (transform.py:303-315).  potential != 0 scales every mode by 1/k^2 (generate.py:200-215).
+ * Output: this rank's [nx][ny/world][nz/2] block in RF_BUF_FIELD. */
+int rf_generate_xpass(rf_ctx* ctx, uint64_t seed, int potential);
+
+/* Passes 2+3 (axis 1, then c2r along axis 2).  For world > 1 the caller first exchanges
+ * RF_BUF_FIELD -> RF_BUF_RECV with an all-to-all of world equal blocks.  zscale (nz host
+ * doubles or NULL) multiplies the output per z index (generate.py:341-343); want_stats
+ * accumulates sum / sum-of-squares of the unscaled field (generate.py:219). */
+int rf_finish_yz(rf_ctx* ctx, const double* zscale, int want_stats);
+
+/* single-GPU convenience: rf_generate_xpass + rf_finish_yz */
+int rf_generate_delta(rf_ctx* ctx, uint64_t seed, int potential, const double* zscale,
+                      int want_stats);
+
+/* np.std(delta.flat) ingredients (generate.py:219): local sum, sum of squares, count.
+ * Synchronises the stream. */
+int rf_stats(rf_ctx* ctx, double* sum, double* sumsq, long long* count);
+
+/* convert_delta_to_density (generate.py:266-273) incl. apply_lognormal_transform
+ * (cosmotools.py:214-221), in place on the real field; growth / rho: nz host doubles. */
+int rf_density(rf_ctx* ctx, int lognormal, double sigma, const double* growth,
+               const double* rho);
+
+/* copy this rank's real field [nx/world][ny][nz] to host memory (synchronous) */
+int rf_copy_field(rf_ctx* ctx, void* host_dst);
+/* element count of this rank's real field */
+long long rf_field_elems(rf_ctx* ctx);
+
+/* Stage-level access for tests and for the Generator.potential / plan_c2r.data_in
+ * attributes: the symmetrised k-space field in the public (nx, ny, nz/2+1) layout and the
+ * reference normalisation, copied to host.  bins (optional) receives the canonical
+ * sigma-table bin index of every mode. */
+int rf_kspace_public(rf_ctx* ctx, uint64_t seed, int potential, void* host_cplx,
+                     int32_t* host_bins);
+
+/* transform.Plan.execute (transform.py:303-315) on host arrays: inverse/forward,
+ * packed (c2r / r2c with the nz/2+1 layout) or unpacked (c2c), numpy normalisation.
+ * in/out are dense C-order host arrays:
+ *   inverse packed : in complex (nx,ny,nz/2+1) -> out real (nx,ny,nz)
+ *   forward packed : in real (nx,ny,nz)        -> out complex (nx,ny,nz/2+1)
+ *   unpacked       : complex (nx,ny,nz) -> complex (nx,ny,nz) */
+int rf_plan_execute(int nx, int ny, int nz, int dtype, int inverse, int packed,
+                    const void* host_in, void* host_out);
+
+/* stage functions on host arrays in the public layout (ncols = nz/2+1 if packed else nz):
+ * powertools.fill_with_log10k (powertools.py:40-61), powertools.tabulate_sigmas
+ * (powertools.py:155-163; table = log10 k, sigma), random.randomize (random.py:12-29,
+ * Philox instead of MT19937), transform.symmetrize (transform.py:114-158). */
+int rf_stage_fill_log10k(int nx, int ny, int nz, int packed, int dtype, double spacing,
+                         void* host_cplx);
+int rf_stage_tabulate(long long nelem, int dtype, int n, const double* log10k,
+                      const double* sigma, void* host_cplx);
+int rf_stage_randomize(long long nelem, int dtype, uint64_t seed, void* host_cplx);
+int rf_stage_symmetrize(int nx, int ny, int nz, int packed, int dtype, void* host_cplx);
+
+/* page-locked host memory for result arrays (transform.allocate, transform.py:10-43, uses
+ * SIMD-aligned memory for the same reason: fast transfers into the transform) */
+void* rf_host_alloc(long long bytes);
+void rf_host_free(void* p);
+
+/* raw device pointers for zero-copy wrapping (torch / DLPack) and for the all-to-all */
+void* rf_device_ptr(rf_ctx* ctx, int which);
+long long rf_buffer_bytes(rf_ctx* ctx, int which);
+/* 1 if the (nx, ny, nz, dtype) grid runs on the tile kernels, 0 if on the generic path */
+int rf_is_fast(rf_ctx* ctx);
+/* number of kernels launched by this context so far */
+long long rf_launch_count(rf_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RF_B200_H */

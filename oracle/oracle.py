@@ -1,0 +1,427 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU oracle for the seed -> delta(x) path.  Never imported by the
+product package (randomfield_b200/); only tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs may use it, and only as the checker or the timed CPU arm.
+
+Part 1 restates, in plain numpy, the reference algorithm (dkirkby/randomfield @ aa97035):
+every function cites the reference file:line it follows.  Parity status: PINNED -- the
+restatement is checked bit-for-bit against the unmodified reference modules run in the build
+container (oracle/ref_replay.py, tests/test_oracle_vs_reference.py) and against the golden
+fixtures committed under tests/golden/ (generated from the reference by
+tests/golden/make_golden.py).  The reference's own tests hold no stored vectors; its
+known-answer test (tests/test_generate.py:24-62, Gaussian-P(k) variance) is re-hosted in
+tests/test_oracle.py.
+
+Part 2 restates the parts of the B200 design that have no counterpart in the reference and
+must be bit-exact on every device: the Philox4x32-10 counter stream and its mode mapping,
+the Hermitian master/slave pairing, and the canonical sigma-table bin index.
+
+Third-party arithmetic the reference delegates to (unvendored, unpinned: numpy >= 1.7,
+scipy): np.fft.irfftn (transform.py:268), RandomState.normal (random.py:24-28),
+np.fft.fftfreq (powertools.py:30-32), scipy interp1d(kind='linear') == np.interp
+(powertools.py:155-157).  This file calls the same numpy routines (numpy 2.3 here).
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+
+_DATA = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                     "randomfield_b200", "data", "default_power.npy")
+
+# ============================================================================================
+# Part 1 -- the reference algorithm
+# ============================================================================================
+
+
+def expanded_shape(data, packed=False):
+    """transform.py:46-60."""
+    nx, ny, nz = data.shape
+    if nx % 2 or ny % 2:
+        raise ValueError('First two dimensions of array must be even.')
+    if packed:
+        if nz % 2 == 0:
+            raise ValueError('Last dimension of packed array must be odd.')
+        nz = 2 * (nz - 1)
+    elif nz % 2:
+        raise ValueError('Last dimension of unpacked array must be even.')
+    return nx, ny, nz
+
+
+def load_default_power():
+    """powertools.py:167-197: the bundled 500-row P(k) table (k in h/Mpc, Pk in (Mpc/h)^3)."""
+    tab = np.load(_DATA)
+    power = np.empty(len(tab), dtype=[('k', float), ('Pk', float)])
+    power['k'], power['Pk'] = tab[:, 0], tab[:, 1]
+    return power
+
+
+def get_k_bounds(shape, spacing):
+    """powertools.py:16-24 for the expanded grid shape."""
+    nx, ny, nz = shape
+    k0 = (2 * np.pi) / spacing
+    return k0 / max(nx, ny, nz), k0 * np.sqrt(3) / 2
+
+
+def create_ksq_grids(shape, spacing, packed=True):
+    """powertools.py:27-37."""
+    nx, ny, nz = shape
+    lambda0 = spacing / (2 * np.pi)
+    kx = np.fft.fftfreq(nx, lambda0)
+    ky = np.fft.fftfreq(ny, lambda0)
+    kz = np.fft.fftfreq(nz, lambda0)
+    if packed:
+        kz = kz[:nz // 2 + 1]
+    return np.meshgrid(kx ** 2, ky ** 2, kz ** 2, sparse=True, indexing='ij')
+
+
+def fill_with_log10k(data, spacing, packed=True):
+    """powertools.py:40-61 (same ufunc calls, so the same mixed f64->f32 rounding)."""
+    shape = expanded_shape(data, packed)
+    kx2, ky2, kz2 = create_ksq_grids(shape, spacing, packed)
+    data.imag = 0
+    np.add(kx2, ky2, out=data.real)
+    np.add(data.real, kz2, out=data.real)
+    old = np.seterr(divide='ignore')
+    np.log10(data.real, out=data.real)
+    np.seterr(**old)
+    data.real *= 0.5
+    return data
+
+
+def validate_power(power):
+    """powertools.py:64-82."""
+    if not isinstance(power, np.ndarray):
+        raise ValueError('Invalid type for power: {0}.'.format(type(power)))
+    if 'k' not in power.dtype.names or 'Pk' not in power.dtype.names:
+        raise ValueError('Missing required fields "k", "Pk" in power.')
+    if not np.all(np.isfinite(power['k'])):
+        raise ValueError('Power spectrum has some invalid values of k.')
+    if not np.all(np.isfinite(power['Pk'])):
+        raise ValueError('Power spectrum has some invalid values of P(k).')
+    if not np.array_equal(power['k'], np.unique(power['k'])):
+        raise ValueError('Power spectrum k values are not strictly increasing.')
+    if power['k'][0] <= 0:
+        raise ValueError('Power spectrum min(k) is <= 0.')
+    if np.any(power['Pk'] < 0):
+        raise ValueError('Power values P(k) are not all non-negative.')
+    return power
+
+
+def filter_power(power, sigma):
+    """powertools.py:85-122 (out=None branch)."""
+    if sigma < 0:
+        raise ValueError('Invalid smoothing sigma: {0}.'.format(sigma))
+    out = np.copy(power)
+    if sigma > 0:
+        out['Pk'] *= np.exp(-(power['k'] * sigma) ** 2)
+    return out
+
+
+def sigma_table(power, shape, spacing):
+    """powertools.py:139-154: (log10 k, sigma) knots, with the k-range check."""
+    nx, ny, nz = shape
+    N3 = nx * ny * nz
+    Vbox = N3 * spacing ** 3
+    pk_min, pk_max = np.min(power['k']), np.max(power['k'])
+    if pk_min <= 0:
+        raise ValueError('Power uses min(k) <= 0: {0}.'.format(pk_min))
+    dk_min, dk_max = get_k_bounds(shape, spacing)
+    if pk_min > dk_min or pk_max < dk_max:
+        raise ValueError('Power k range [{0}:{1}] does not cover data k range [{2}:{3}].'
+                         .format(pk_min, pk_max, dk_min, dk_max))
+    return np.log10(power['k']), N3 * np.sqrt(power['Pk'] / (2 * Vbox))
+
+
+def tabulate_sigmas(data, power, spacing, packed=True):
+    """powertools.py:125-164.  interp1d(kind='linear', bounds_error=False, fill_value=0)
+    evaluates exactly like np.interp(..., left=0, right=0) (scipy delegates to it)."""
+    validate_power(power)
+    shape = expanded_shape(data, packed)
+    log10_k, sigma = sigma_table(power, shape, spacing)
+    data.real = np.interp(data.real, log10_k, sigma, left=0.0, right=0.0)
+    return data
+
+
+def randomize(data, seed=None, noise=None):
+    """random.py:12-29.  `noise` (2*data.size float64 values) replaces the
+    RandomState(seed).normal draw so the same deviates can be injected elsewhere."""
+    data.imag = data.real
+    real_type = np.float32 if data.dtype == np.complex64 else np.float64
+    sigmas = data.view(real_type).reshape(2 * data.size)
+    if noise is None:
+        noise = np.random.RandomState(seed).normal(size=2 * data.size)
+    sigmas *= np.asarray(noise, dtype=np.float64).reshape(-1)
+    return data
+
+
+def symmetrize(data, packed=False):
+    """transform.py:114-158, same statement order."""
+    nx, ny, nz = expanded_shape(data, packed=packed)
+    xlo, xhi = slice(1, nx // 2), slice(nx - 1, nx // 2, -1)
+    ylo, yhi = slice(1, ny // 2), slice(ny - 1, ny // 2, -1)
+    hx, hy, hz = nx // 2, ny // 2, nz // 2
+    if not packed:
+        zlo, zhi = slice(1, hz), slice(nz - 1, hz, -1)
+        data[xhi, yhi, zhi] = np.conj(data[xlo, ylo, zlo])
+        data[xlo, yhi, zhi] = np.conj(data[xhi, ylo, zlo])
+        data[xhi, ylo, zhi] = np.conj(data[xlo, yhi, zlo])
+        data[xhi, yhi, zlo] = np.conj(data[xlo, ylo, zhi])
+        data[[0, hx], ylo, zhi] = np.conj(data[[0, hx], yhi, zlo])
+        data[[0, hx], yhi, zhi] = np.conj(data[[0, hx], ylo, zlo])
+        data[xlo, [0, hy], zhi] = np.conj(data[xhi, [0, hy], zlo])
+        data[xhi, [0, hy], zhi] = np.conj(data[xlo, [0, hy], zlo])
+        data[[0, 0, hx, hx], [0, hy, 0, hy], zhi] = np.conj(data[[0, 0, hx, hx], [0, hy, 0, hy], zlo])
+    data[xlo, yhi, [0, hz]] = np.conj(data[xhi, ylo, [0, hz]])
+    data[xhi, yhi, [0, hz]] = np.conj(data[xlo, ylo, [0, hz]])
+    data[[0, 0, hx, hx], yhi, [0, hz, 0, hz]] = np.conj(data[[0, 0, hx, hx], ylo, [0, hz, 0, hz]])
+    data[xhi, [0, 0, hy, hy], [0, hz, 0, hz]] = np.conj(data[xlo, [0, 0, hy, hy], [0, hz, 0, hz]])
+    data.imag[[0, 0, 0, 0, hx, hx, hx, hx], [0, 0, hy, hy, 0, 0, hy, hy],
+              [0, hz, 0, hz, 0, hz, 0, hz]] = 0
+    data.real[0, 0, 0] = 0
+    return data
+
+
+def is_hermitian(data, packed=False, rtol=1e-08, atol=1e-08):
+    """transform.py:93-111."""
+    nx, ny, nz = expanded_shape(data, packed=packed)
+    z_range = [0, nz // 2] if packed else range(nz // 2 + 1)
+    for ix in range(nx // 2 + 1):
+        jx = (nx - ix) % nx
+        for iy in range(ny // 2 + 1):
+            jy = (ny - iy) % ny
+            for iz in z_range:
+                jz = (nz - iz) % nz
+                if not np.allclose(data[ix, iy, iz], np.conj(data[jx, jy, jz]), rtol, atol):
+                    return False
+    return True
+
+
+def potential_from_kfield(kfield, spacing):
+    """generate.py:200-215: delta(k) / k^2 with the same f32 ufunc sequence."""
+    shape = expanded_shape(kfield, packed=True)
+    potential = np.empty_like(kfield)
+    potential.imag = 0.
+    kx2, ky2, kz2 = create_ksq_grids(shape, spacing, packed=True)
+    np.add(kx2, ky2, out=potential.real)
+    potential.real += kz2
+    old = np.seterr(divide='ignore')
+    np.reciprocal(potential.real, out=potential.real)
+    np.seterr(**old)
+    potential[0, 0, 0] = 0.
+    potential *= kfield
+    return potential
+
+
+def c2r(kfield, shape):
+    """transform.Plan.execute, numpy branch (transform.py:266-270, 311-314)."""
+    return np.fft.irfftn(kfield, s=shape, axes=(0, 1, 2))
+
+
+def generate_kfield(shape, spacing, power, seed=None, smoothing=0.0, dtype=np.complex64, noise=None):
+    """generate.py:191-199: the symmetrised k-space field just before the transform."""
+    nx, ny, nz = shape
+    data = np.empty((nx, ny, nz // 2 + 1), dtype=dtype)
+    fill_with_log10k(data, spacing, packed=True)
+    smoothed = filter_power(power, smoothing)
+    tabulate_sigmas(data, smoothed, spacing, packed=True)
+    randomize(data, seed=seed, noise=noise)
+    symmetrize(data, packed=True)
+    return data
+
+
+def generate_delta_field(shape, spacing, power, seed=None, smoothing=0.0, dtype=np.complex64,
+                         noise=None, save_potential=False):
+    """generate.py:191-219.  Returns dict(delta, rms, kfield, potential)."""
+    kfield = generate_kfield(shape, spacing, power, seed, smoothing, dtype, noise)
+    potential = potential_from_kfield(kfield, spacing) if save_potential else None
+    real_type = np.float32 if np.dtype(dtype) == np.complex64 else np.float64
+    delta = np.empty(shape, dtype=real_type)
+    delta[:] = c2r(kfield, shape)
+    return dict(delta=delta, rms=np.std(delta.flat), kfield=kfield, potential=potential)
+
+
+def apply_lognormal_transform(delta, growth, sigma=None):
+    """cosmotools.py:206-221 (in place, same op order)."""
+    if sigma is None:
+        sigma = np.std(delta)
+    t = 1 + (sigma * growth) ** 2
+    delta /= sigma
+    delta *= np.sqrt(np.log(t))
+    delta = np.exp(delta, out=delta)
+    delta /= np.sqrt(t)
+    return delta
+
+
+def convert_delta_to_density(delta, growth, mean_density, sigma, lognormal=True):
+    """generate.py:266-273; growth / mean_density broadcast along the last axis."""
+    if lognormal:
+        delta = apply_lognormal_transform(delta, growth, sigma=sigma)
+    else:
+        delta *= growth
+        delta += 1
+    delta *= mean_density
+    return delta
+
+
+H0_PER_S = 100.0 * 1.0e3 / 3.0856775814913673e22   # 100 km/s/Mpc in 1/s
+
+
+def newtonian_potential(potential, shape, Om0, growth=None, redshifts=None):
+    """generate.py:331-343: c2r(potential * scale) [* G(z) / (1+z)]."""
+    scale = -1.5 * H0_PER_S ** 2 * Om0
+    data_in = potential.copy()
+    data_in *= scale
+    real_type = np.float32 if potential.dtype == np.complex64 else np.float64
+    field = np.empty(shape, dtype=real_type)
+    field[:] = c2r(data_in, shape)
+    if growth is not None:
+        field *= growth
+        field /= 1 + redshifts
+    return field
+
+
+# ============================================================================================
+# Part 2 -- B200-design pieces that must be bit-exact
+# ============================================================================================
+
+_M0, _M1 = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57)
+_W0, _W1 = 0x9E3779B9, 0xBB67AE85
+_MASK = np.uint64(0xFFFFFFFF)
+_S32 = np.uint64(32)
+
+
+def philox4x32_10(c0, c1, c2, c3, k0, k1):
+    """Philox4x32-10 (Salmon, Moraes, Dror, Shaw, SC'11), vectorised over uint64-held
+    32-bit lanes.  Returns four uint32 arrays."""
+    c0, c1, c2, c3 = (np.asarray(c, dtype=np.uint64) & _MASK for c in (c0, c1, c2, c3))
+    c0, c1, c2, c3 = np.broadcast_arrays(c0, c1, c2, c3)
+    k0, k1 = int(k0) & 0xFFFFFFFF, int(k1) & 0xFFFFFFFF
+    for _ in range(10):
+        p0 = _M0 * c0
+        p1 = _M1 * c2
+        n0 = (p1 >> _S32) ^ c1 ^ np.uint64(k0)
+        n1 = p1 & _MASK
+        n2 = (p0 >> _S32) ^ c3 ^ np.uint64(k1)
+        n3 = p0 & _MASK
+        c0, c1, c2, c3 = n0, n1, n2, n3
+        k0 = (k0 + _W0) & 0xFFFFFFFF
+        k1 = (k1 + _W1) & 0xFFFFFFFF
+    return tuple(c.astype(np.uint32) for c in (c0, c1, c2, c3))
+
+
+def philox_words(shape, seed, iy_range=None):
+    """The two 32-bit words (wa, wb) that serve each mode of the public (nx, ny, nz/2+1)
+    array: counter q = ((ix mod nx/2)*ny + iy)*(nz/2+1) + iz, key = seed; words (0,1) serve
+    ix < nx/2 and words (2,3) serve ix >= nx/2 (rf_common.cuh raw_mode)."""
+    nx, ny, nz = shape
+    nzh = nz // 2 + 1
+    y0, y1 = iy_range if iy_range is not None else (0, ny)
+    px = np.arange(nx // 2, dtype=np.uint64)[:, None, None]
+    iy = np.arange(y0, y1, dtype=np.uint64)[None, :, None]
+    iz = np.arange(nzh, dtype=np.uint64)[None, None, :]
+    q = (px * np.uint64(ny) + iy) * np.uint64(nzh) + iz
+    seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+    w = philox4x32_10(q & _MASK, q >> _S32, 0, 0, seed & 0xFFFFFFFF, seed >> 32)
+    wa = np.concatenate([w[0], w[2]], axis=0)
+    wb = np.concatenate([w[1], w[3]], axis=0)
+    return wa, wb
+
+
+def box_muller(wa, wb):
+    """(wa, wb) -> complex standard normal: u1 = ((wa>>9)+0.5)/2^23, angle = pi*int32(wb)/2^31."""
+    u1 = ((wa >> np.uint32(9)).astype(np.float64) + 0.5) / 8388608.0
+    r = np.sqrt(-2.0 * np.log(u1))
+    ang = np.pi * wb.astype(np.int32).astype(np.float64) / 2147483648.0
+    return r * np.cos(ang) + 1j * (r * np.sin(ang))
+
+
+def hermitian_pairing(shape):
+    """Master index of every element on the planes iz in {0, nz/2} of the public packed
+    layout: returns (mx, my, conj, vertex) arrays of shape (nx, ny).  An element is a slave
+    iff iy > ny/2, or iy in {0, ny/2} and ix > nx/2; master = ((nx-ix)%nx, (ny-iy)%ny)."""
+    nx, ny, nz = shape
+    ix = np.arange(nx)[:, None] + np.zeros((1, ny), dtype=int)
+    iy = np.arange(ny)[None, :] + np.zeros((nx, 1), dtype=int)
+    yedge = (iy == 0) | (iy == ny // 2)
+    slave = (iy > ny // 2) | (yedge & (ix > nx // 2))
+    mx = np.where(slave, (nx - ix) % nx, ix)
+    my = np.where(slave, (ny - iy) % ny, iy)
+    vertex = yedge & ((ix == 0) | (ix == nx // 2))
+    return mx, my, slave, vertex
+
+
+def canonical_ksq(shape, spacing, real_type=np.float32, iy_range=None):
+    """k^2 = fma(jx^2, k0x^2, fma(jy^2, k0y^2, jz^2*k0z^2)) evaluated in `real_type` with
+    single roundings (rf_common.cuh ksq_canon).  fma is emulated exactly: products of two
+    f32 are exact in f64 and |sum| stays far below 2^53 ulps, so f64 add + one rounding to f32
+    equals the fused result except for double rounding, which we remove by computing in
+    longdouble for f64."""
+    nx, ny, nz = shape
+    nzh = nz // 2 + 1
+    T = np.dtype(real_type).type
+    k0sq = [T((2 * np.pi / (n * spacing)) ** 2) for n in (nx, ny, nz)]
+
+    def jsq(n, lo=0, hi=None):
+        i = np.arange(lo, n if hi is None else hi)
+        j = np.where(i <= n // 2, i, i - n)
+        return (j * j).astype(real_type)
+
+    y0, y1 = iy_range if iy_range is not None else (0, ny)
+    jx2 = jsq(nx)[:, None, None]
+    jy2 = jsq(ny, y0, y1)[None, :, None]
+    jz2 = jsq(nz, 0, nzh)[None, None, :]
+    wide = np.float64 if T is np.float32 else np.longdouble
+    inner0 = (jz2.astype(wide) * wide(k0sq[2])).astype(real_type)                     # fmul_rn
+    inner1 = (jy2.astype(wide) * wide(k0sq[1]) + inner0.astype(wide)).astype(real_type)  # fma_rn
+    ksq = (jx2.astype(wide) * wide(k0sq[0]) + inner1.astype(wide)).astype(real_type)     # fma_rn
+    return ksq
+
+
+def canonical_bins(ksq, k_table, real_type=np.float32):
+    """Largest j with T(k_j^2) <= ksq, or -1 (rf_common.cuh sigma_bin)."""
+    edges = (np.asarray(k_table, dtype=np.float64) ** 2).astype(real_type)
+    return (np.searchsorted(edges, ksq, side='right') - 1).astype(np.int32)
+
+
+def philox_sigma(ksq, bins, k_table, sigma_table_ref, shape, real_type=np.float64):
+    """sigma(k) of the CUDA path evaluated in float64: linear in log2(k^2) on segment `bins`,
+    zero outside the table.  sigma_table_ref is in the reference normalisation."""
+    k = np.asarray(k_table, dtype=np.float64)
+    n = len(k)
+    l2 = 2.0 * np.log2(k)
+    sg = np.asarray(sigma_table_ref, dtype=np.float64)
+    seg = np.clip(bins, 0, n - 2)
+    slope = (sg[1:] - sg[:-1]) / (l2[1:] - l2[:-1])
+    edges_last = (k[-1] ** 2).astype(ksq.dtype) if hasattr(k[-1] ** 2, 'astype') else ksq.dtype.type(k[-1] ** 2)
+    outside = (bins < 0) | ((bins == n - 1) & (ksq > edges_last))
+    with np.errstate(divide='ignore', invalid='ignore'):
+        val = sg[seg] + slope[seg] * (np.log2(ksq.astype(np.float64)) - l2[seg])
+    return np.where(outside, 0.0, val)
+
+
+def philox_kfield(shape, spacing, power, seed, smoothing=0.0, potential=False):
+    """The symmetrised k-space field of the CUDA Philox path in the public layout and the
+    reference normalisation, evaluated in float64 (bins and k^2 are the float32 canonical
+    ones, as on the device).  Used to check the device field to rounding error."""
+    nx, ny, nz = shape
+    nzh = nz // 2 + 1
+    smoothed = filter_power(power, smoothing)
+    _, sig_tab = sigma_table(smoothed, shape, spacing)
+    ksq = canonical_ksq(shape, spacing, np.float32)
+    bins = canonical_bins(ksq, smoothed['k'], np.float32)
+    sig = philox_sigma(ksq, bins, smoothed['k'], sig_tab, shape)
+    if potential:
+        with np.errstate(divide='ignore', invalid='ignore'):
+            sig = np.where(ksq > 0, sig / ksq.astype(np.float64), 0.0)
+    wa, wb = philox_words(shape, seed)
+    raw = sig * box_muller(wa, wb)
+    out = raw.copy()
+    mx, my, slave, vertex = hermitian_pairing(shape)
+    for iz in (0, nz // 2):
+        plane = raw[mx, my, iz]
+        plane = np.where(slave, np.conj(plane), plane)
+        plane = np.where(vertex, plane.real + 0j, plane)
+        out[:, :, iz] = plane
+    out[0, 0, 0] = 0.0
+    return out, bins

@@ -1,0 +1,117 @@
+"""TEST INFRASTRUCTURE ONLY -- loads the UNMODIFIED reference modules from /root/reference.
+
+Only usable in the build container (the GPU box has no /root/reference).  It exists to
+(1) pin the numpy restatement in oracle/oracle.py against the real reference and
+(2) generate the golden fixtures under tests/golden/ (tests/golden/make_golden.py).
+
+The reference is Python-2 era: transform.py / powertools.py / random.py import each other
+with implicit-relative imports and use numpy names removed in numpy 2.  We load them by file
+path under their bare names, after defining the removed aliases.
+generate.py and cosmotools.py cannot be imported (astropy is absent), so replay() restates
+the nine calls of generate.py:191-219 against the loaded modules.
+"""
+from __future__ import annotations
+
+import importlib.util
+import os
+import sys
+
+import numpy as np
+
+REFERENCE_ROOT = os.environ.get("RF_REFERENCE_ROOT", "/root/reference")
+_PKG = os.path.join(REFERENCE_ROOT, "randomfield")
+_mods = {}
+
+
+def available() -> bool:
+    return os.path.exists(os.path.join(_PKG, "transform.py"))
+
+
+def _shim_numpy():
+    aliases = {
+        "complex_": np.complex128, "float_": np.float64, "clongfloat": np.clongdouble,
+        "longfloat": np.longdouble, "float": float, "int": int,
+    }
+    for name, val in aliases.items():
+        if not hasattr(np, name):
+            setattr(np, name, val)
+    if not hasattr(np, "obj2sctype"):
+        def obj2sctype(rep, default=None):
+            try:
+                if isinstance(rep, np.ndarray):
+                    return rep.dtype.type
+                return np.dtype(rep).type
+            except Exception:
+                return default
+        np.obj2sctype = obj2sctype
+
+
+def _load(name, filename, as_name=None):
+    spec = importlib.util.spec_from_file_location(as_name or name, os.path.join(_PKG, filename))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[as_name or name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def modules():
+    """Return (transform, powertools, random) reference modules."""
+    if not _mods:
+        if not available():
+            raise RuntimeError("reference tree not found at %s" % REFERENCE_ROOT)
+        _shim_numpy()
+        # the reference re-imports itself by bare name at call time (powertools.py:185), so the
+        # bare names stay registered; the product lives under randomfield_b200.* and never
+        # uses them
+        _mods["transform"] = _load("transform", "transform.py")
+        _mods["powertools"] = _load("powertools", "powertools.py")
+        _mods["random"] = _load("rf_ref_random", "random.py", as_name="rf_ref_random")
+    return _mods["transform"], _mods["powertools"], _mods["random"]
+
+
+def replay(nx, ny, nz, spacing, seed=None, smoothing=0.0, power=None, dtype=np.complex64,
+           noise=None, save_potential=False):
+    """Replay generate.py:191-219 on the reference modules.
+
+    Returns dict(delta, rms, kfield (copy before the transform), potential (or None)).
+    If `noise` is given it replaces RandomState(seed).normal(size) (random.py:24-28) so
+    the same white noise can be injected into the CUDA path.
+    """
+    transform, powertools, rrandom = modules()
+    plan = transform.Plan(shape=(nx, ny, nz), dtype_in=dtype, packed=True, overwrite=True,
+                          inverse=True, use_pyfftw=True)
+    if power is None:
+        power = powertools.load_default_power()
+    powertools.fill_with_log10k(plan.data_in, spacing=spacing, packed=True)
+    smoothed = powertools.filter_power(power, smoothing)
+    powertools.tabulate_sigmas(plan.data_in, power=smoothed, spacing=spacing, packed=True)
+    if noise is None:
+        rrandom.randomize(plan.data_in, seed=seed)
+    else:
+        # random.py:17-28 with the deviates supplied by the caller
+        plan.data_in.imag = plan.data_in.real
+        real_type = transform.scalar_type(plan.data_in.dtype)
+        sigmas = plan.data_in.view(real_type).reshape(2 * plan.data_in.size)
+        sigmas *= np.asarray(noise, dtype=np.float64).reshape(-1)
+    transform.symmetrize(plan.data_in, packed=True)
+    kfield = plan.data_in.copy()
+    potential = None
+    if save_potential:
+        # generate.py:200-215
+        potential = np.empty_like(plan.data_in)
+        potential.imag = 0.
+        kx2, ky2, kz2 = powertools.create_ksq_grids(potential, spacing=spacing, packed=True)
+        np.add(kx2, ky2, out=potential.real)
+        potential.real += kz2
+        old = np.seterr(divide='ignore')
+        np.reciprocal(potential.real, out=potential.real)
+        np.seterr(**old)
+        potential[0, 0, 0] = 0.
+        potential *= plan.data_in
+    delta = plan.execute()
+    rms = np.std(delta.flat)
+    return dict(delta=np.array(delta), rms=rms, kfield=kfield, potential=potential)
+
+
+def default_power():
+    return modules()[1].load_default_power()

@@ -1,0 +1,247 @@
+"""ctypes binding to librf_b200.so (include/rf_b200.h).
+
+The product path has no CPU implementation: if the shared library is missing, or no CUDA
+device is visible when a context is created, the calls below raise.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librf_b200.so")
+
+RF_F32, RF_F64 = 0, 1
+RF_BUF_FIELD, RF_BUF_RECV, RF_BUF_PARTIALS = 0, 1, 2
+RF_ERR_ARG, RF_ERR_CUDA, RF_ERR_STATE = -1, -2, -3
+
+# every symbol include/rf_b200.h declares: (name, restype, argtypes)
+_c = ctypes
+_P = _c.c_void_p
+SIGNATURES = {
+    "rf_last_error": (_c.c_char_p, []),
+    "rf_version": (_c.c_int, []),
+    "rf_create": (_c.c_int, [_c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.POINTER(_P)]),
+    "rf_destroy": (_c.c_int, [_P]),
+    "rf_set_stream": (_c.c_int, [_P, _P]),
+    "rf_sync": (_c.c_int, [_P]),
+    "rf_set_power": (_c.c_int, [_P, _c.c_int, _P, _P, _c.c_double]),
+    "rf_set_noise": (_c.c_int, [_P, _P]),
+    "rf_generate_xpass": (_c.c_int, [_P, _c.c_uint64, _c.c_int]),
+    "rf_finish_yz": (_c.c_int, [_P, _P, _c.c_int]),
+    "rf_generate_delta": (_c.c_int, [_P, _c.c_uint64, _c.c_int, _P, _c.c_int]),
+    "rf_stats": (_c.c_int, [_P, _c.POINTER(_c.c_double), _c.POINTER(_c.c_double), _c.POINTER(_c.c_longlong)]),
+    "rf_density": (_c.c_int, [_P, _c.c_int, _c.c_double, _P, _P]),
+    "rf_copy_field": (_c.c_int, [_P, _P]),
+    "rf_field_elems": (_c.c_longlong, [_P]),
+    "rf_kspace_public": (_c.c_int, [_P, _c.c_uint64, _c.c_int, _P, _P]),
+    "rf_plan_execute": (_c.c_int, [_c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P, _P]),
+    "rf_stage_fill_log10k": (_c.c_int, [_c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _P]),
+    "rf_stage_tabulate": (_c.c_int, [_c.c_longlong, _c.c_int, _c.c_int, _P, _P, _P]),
+    "rf_stage_randomize": (_c.c_int, [_c.c_longlong, _c.c_int, _c.c_uint64, _P]),
+    "rf_stage_symmetrize": (_c.c_int, [_c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P]),
+    "rf_host_alloc": (_P, [_c.c_longlong]),
+    "rf_host_free": (None, [_P]),
+    "rf_device_ptr": (_P, [_P, _c.c_int]),
+    "rf_buffer_bytes": (_c.c_longlong, [_P, _c.c_int]),
+    "rf_is_fast": (_c.c_int, [_P]),
+    "rf_launch_count": (_c.c_longlong, [_P]),
+}
+
+_LIB = None
+
+
+def lib():
+    """Load librf_b200.so (once).  Raises if it has not been built."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "librf_b200.so is missing (%s): build it with `python -m randomfield_b200.build`; "
+                "randomfield_b200 has no CPU fallback." % LIB_PATH)
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = handle
+    return _LIB
+
+
+def last_error() -> str:
+    msg = lib().rf_last_error()
+    return msg.decode() if msg else ""
+
+
+def check(status: int, value_error_ok: bool = True):
+    """Map a C status to the exception types the reference raises."""
+    if status == 0:
+        return
+    msg = last_error()
+    if status == RF_ERR_ARG and value_error_ok:
+        raise ValueError(msg)
+    raise RuntimeError(msg or "librf_b200 call failed with status %d" % status)
+
+
+def dtype_code(dtype) -> int:
+    dt = np.dtype(dtype)
+    if dt in (np.dtype(np.float32), np.dtype(np.complex64)):
+        return RF_F32
+    if dt in (np.dtype(np.float64), np.dtype(np.complex128)):
+        return RF_F64
+    raise ValueError("Unsupported dtype for the B200 path: {0}.".format(dt))
+
+
+def ptr(arr: np.ndarray):
+    return arr.ctypes.data_as(ctypes.c_void_p)
+
+
+class PinnedArray:
+    """numpy array over page-locked host memory owned by the library."""
+
+    def __init__(self, shape, dtype):
+        self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self._p = lib().rf_host_alloc(self.nbytes)
+        if not self._p:
+            raise MemoryError(last_error())
+        buf = (ctypes.c_char * self.nbytes).from_address(self._p)
+        self.array = np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_p", None):
+                lib().rf_host_free(self._p)
+                self._p = None
+        except Exception:
+            pass
+
+
+class Engine:
+    """One rf_ctx: the device side of a Generator (one rank of a slab decomposition)."""
+
+    def __init__(self, nx, ny, nz, dtype=np.float32, rank=0, world=1):
+        self.nx, self.ny, self.nz = int(nx), int(ny), int(nz)
+        self.real_dtype = np.dtype(np.float32 if dtype_code(dtype) == RF_F32 else np.float64)
+        self.complex_dtype = np.dtype(np.complex64 if self.real_dtype == np.float32 else np.complex128)
+        self.rank, self.world = int(rank), int(world)
+        self._ctx = ctypes.c_void_p()
+        check(lib().rf_create(self.nx, self.ny, self.nz, dtype_code(dtype), self.rank, self.world,
+                              ctypes.byref(self._ctx)))
+        self.nxl, self.nyl = self.nx // self.world, self.ny // self.world
+
+    # -- lifetime ---------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_ctx", None) is not None and self._ctx:
+            lib().rf_destroy(self._ctx)
+            self._ctx = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- configuration ------------------------------------------------------------------
+    def set_stream(self, cuda_stream_handle):
+        check(lib().rf_set_stream(self._ctx, ctypes.c_void_p(cuda_stream_handle or 0)))
+
+    def set_power(self, k, sigma, spacing):
+        k = np.ascontiguousarray(k, dtype=np.float64)
+        sigma = np.ascontiguousarray(sigma, dtype=np.float64)
+        check(lib().rf_set_power(self._ctx, len(k), ptr(k), ptr(sigma), float(spacing)))
+
+    def set_noise(self, noise):
+        if noise is None:
+            check(lib().rf_set_noise(self._ctx, None))
+            return
+        noise = np.ascontiguousarray(noise, dtype=np.float64).reshape(-1)
+        expect = 2 * self.nx * self.ny * (self.nz // 2 + 1)
+        if noise.size != expect:
+            raise ValueError("noise has {0} values, expected {1}.".format(noise.size, expect))
+        check(lib().rf_set_noise(self._ctx, ptr(noise)))
+
+    # -- hot path -------------------------------------------------------------------------
+    def generate_xpass(self, seed, potential=False):
+        check(lib().rf_generate_xpass(self._ctx, int(seed) & 0xFFFFFFFFFFFFFFFF, int(bool(potential))))
+
+    def finish_yz(self, zscale=None, want_stats=True):
+        zs = None if zscale is None else np.ascontiguousarray(zscale, dtype=np.float64)
+        check(lib().rf_finish_yz(self._ctx, None if zs is None else ptr(zs), int(bool(want_stats))))
+
+    def generate_delta(self, seed, potential=False, zscale=None, want_stats=True):
+        zs = None if zscale is None else np.ascontiguousarray(zscale, dtype=np.float64)
+        check(lib().rf_generate_delta(self._ctx, int(seed) & 0xFFFFFFFFFFFFFFFF, int(bool(potential)),
+                                      None if zs is None else ptr(zs), int(bool(want_stats))))
+
+    def stats(self):
+        s1, s2, n = ctypes.c_double(), ctypes.c_double(), ctypes.c_longlong()
+        check(lib().rf_stats(self._ctx, ctypes.byref(s1), ctypes.byref(s2), ctypes.byref(n)),
+              value_error_ok=False)
+        return s1.value, s2.value, n.value
+
+    def density(self, lognormal, sigma, growth, rho):
+        g = np.ascontiguousarray(np.broadcast_to(np.asarray(growth, dtype=np.float64).reshape(-1), (self.nz,)))
+        r = np.ascontiguousarray(np.broadcast_to(np.asarray(rho, dtype=np.float64).reshape(-1), (self.nz,)))
+        check(lib().rf_density(self._ctx, int(bool(lognormal)), float(sigma), ptr(g), ptr(r)))
+
+    def sync(self):
+        check(lib().rf_sync(self._ctx))
+
+    # -- data movement ------------------------------------------------------------------------
+    @property
+    def field_shape(self):
+        return (self.nxl, self.ny, self.nz)
+
+    def copy_field(self, out=None):
+        if out is None:
+            out = np.empty(self.field_shape, dtype=self.real_dtype)
+        if out.dtype != self.real_dtype or out.shape != self.field_shape or not out.flags.c_contiguous:
+            raise ValueError("bad output array for copy_field")
+        check(lib().rf_copy_field(self._ctx, ptr(out)), value_error_ok=False)
+        return out
+
+    def kspace_public(self, seed, potential=False, with_bins=False):
+        shape = (self.nx, self.nyl, self.nz // 2 + 1)
+        out = np.empty(shape, dtype=self.complex_dtype)
+        bins = np.empty(shape, dtype=np.int32) if with_bins else None
+        check(lib().rf_kspace_public(self._ctx, int(seed) & 0xFFFFFFFFFFFFFFFF, int(bool(potential)),
+                                     ptr(out), None if bins is None else ptr(bins)))
+        return (out, bins) if with_bins else out
+
+    def device_ptr(self, which=RF_BUF_FIELD):
+        return lib().rf_device_ptr(self._ctx, which)
+
+    def buffer_bytes(self, which=RF_BUF_FIELD):
+        return lib().rf_buffer_bytes(self._ctx, which)
+
+    @property
+    def is_fast(self):
+        return bool(lib().rf_is_fast(self._ctx))
+
+    @property
+    def launch_count(self):
+        return int(lib().rf_launch_count(self._ctx))
+
+    def torch_view(self, which=RF_BUF_FIELD, nbytes=None):
+        """Zero-copy uint8 torch tensor over a library-owned device buffer."""
+        import torch
+
+        class _Holder:
+            pass
+
+        h = _Holder()
+        n = int(nbytes if nbytes is not None else self.buffer_bytes(which))
+        h.__cuda_array_interface__ = {
+            "shape": (n,), "typestr": "|u1", "data": (int(self.device_ptr(which)), False), "version": 2,
+        }
+        return torch.as_tensor(h, device="cuda")
+
+    def field_tensor(self):
+        """The real field [nx/world, ny, nz] as a torch tensor sharing device memory."""
+        import torch
+        n = self.nxl * self.ny * self.nz
+        t = self.torch_view(RF_BUF_FIELD, n * self.real_dtype.itemsize)
+        tdt = torch.float32 if self.real_dtype == np.float32 else torch.float64
+        return t.view(tdt).view(self.nxl, self.ny, self.nz)

@@ -1,0 +1,780 @@
+// rf_api.cu -- context management and the C ABI of librf_b200.so (see include/rf_b200.h).
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/rf_b200.h"
+#include "rf_generic.cuh"
+#include "rf_launch.h"
+
+using namespace rf;
+
+// ------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+
+static int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+#define RF_CUDA(expr)                                                                     \
+  do {                                                                                    \
+    cudaError_t e__ = (cudaError_t)(expr);                                                \
+    if (e__ != cudaSuccess)                                                               \
+      return fail(RF_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));      \
+  } while (0)
+
+extern "C" const char* rf_last_error(void) { return g_err.c_str(); }
+extern "C" int rf_version(void) { return 100; }
+
+// ------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------
+struct rf_ctx {
+  int nx = 0, ny = 0, nz = 0, dtype = 0, rank = 0, world = 1;
+  int nxl = 0, nyl = 0;     // local slab extents
+  bool fast = false;
+  size_t esize = 4;         // sizeof(T)
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  void* field = nullptr;    // RF_BUF_FIELD
+  void* recv = nullptr;     // RF_BUF_RECV (world > 1) or generic-path scratch
+  size_t buf_bytes = 0;
+  double* partials = nullptr;
+  long long nparts = 0, parts_cap = 0;
+  double* stats_dev = nullptr;
+  bool stats_valid = false;
+  // twiddles exp(+2 pi i k / n) per axis (+ nz/2 for the c2r half-length transform)
+  void *tw_x = nullptr, *tw_y = nullptr, *tw_z = nullptr, *tw_zh = nullptr;
+  // sigma table
+  void* knots = nullptr;
+  int16_t* lut = nullptr;
+  int ntab = 0, lut_n = 0, lut_base = 0;
+  double spacing = 0.0;
+  bool have_power = false;
+  double* noise = nullptr;
+  void *zs_dev = nullptr, *da_dev = nullptr, *db_dev = nullptr;   // nz-length tables of T
+  long long launches = 0;
+  bool field_is_real = false;
+};
+
+static bool is_pow2(int n) { return n > 0 && (n & (n - 1)) == 0; }
+static bool fast_size(int n) { return is_pow2(n) && n >= 64 && n <= 4096; }
+
+template <typename T>
+static int upload_twiddles(void** dst, int n) {
+  std::vector<cpx<T>> h(n);
+  for (int k = 0; k < n; ++k) {
+    // exact quadrant reduction through the argument of cos/sin(pi * x)
+    long double a = 2.0L * (long double)k / (long double)n;
+    h[k] = {(T)cosl(M_PIl * a), (T)sinl(M_PIl * a)};
+  }
+  // pin the exactly-representable points
+  h[0] = {(T)1, (T)0};
+  if (n % 2 == 0) h[n / 2] = {(T)-1, (T)0};
+  if (n % 4 == 0) { h[n / 4] = {(T)0, (T)1}; h[3 * n / 4] = {(T)0, (T)-1}; }
+  RF_CUDA(cudaMalloc(dst, sizeof(cpx<T>) * n));
+  RF_CUDA(cudaMemcpy(*dst, h.data(), sizeof(cpx<T>) * n, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+extern "C" int rf_create(int nx, int ny, int nz, int dtype, int rank, int world, rf_ctx** out) {
+  if (!out) return fail(RF_ERR_ARG, "rf_create: out is NULL");
+  if (nx <= 0 || ny <= 0 || nz <= 0 || (nx % 2) || (ny % 2) || (nz % 2))
+    return fail(RF_ERR_ARG, "All shape dimensions must be even.");
+  if (dtype != RF_F32 && dtype != RF_F64) return fail(RF_ERR_ARG, "rf_create: bad dtype");
+  if (world < 1 || rank < 0 || rank >= world) return fail(RF_ERR_ARG, "rf_create: bad rank/world");
+  if (world > 1 && ((nx % world) || (ny % world)))
+    return fail(RF_ERR_ARG, "rf_create: nx and ny must be divisible by world");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return fail(RF_ERR_CUDA, "rf_create: no CUDA device available (this library has no CPU path)");
+  rf_ctx* c = new rf_ctx();
+  c->nx = nx; c->ny = ny; c->nz = nz; c->dtype = dtype; c->rank = rank; c->world = world;
+  c->nxl = nx / world; c->nyl = ny / world;
+  c->esize = dtype == RF_F32 ? 4 : 8;
+  c->fast = fast_size(nx) && fast_size(ny) && fast_size(nz);
+  if (world > 1 && !c->fast) {
+    delete c;
+    return fail(RF_ERR_ARG, "rf_create: slab decomposition needs power-of-two dims in [64, 4096]");
+  }
+  RF_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+  c->stream = c->own_stream;
+  // local k-space block in the public layout is the largest thing we ever hold
+  const size_t nzh = nz / 2 + 1;
+  c->buf_bytes = (size_t)nx * c->nyl * nzh * 2 * c->esize;
+  RF_CUDA(cudaMalloc(&c->field, c->buf_bytes));
+  if (world > 1) RF_CUDA(cudaMalloc(&c->recv, c->buf_bytes));
+  RF_CUDA(cudaMalloc(&c->stats_dev, 2 * sizeof(double)));
+  int e = 0;
+  if (dtype == RF_F32) {
+    e |= upload_twiddles<float>(&c->tw_x, nx);
+    e |= upload_twiddles<float>(&c->tw_y, ny);
+    e |= upload_twiddles<float>(&c->tw_z, nz);
+    e |= upload_twiddles<float>(&c->tw_zh, nz / 2);
+  } else {
+    e |= upload_twiddles<double>(&c->tw_x, nx);
+    e |= upload_twiddles<double>(&c->tw_y, ny);
+    e |= upload_twiddles<double>(&c->tw_z, nz);
+    e |= upload_twiddles<double>(&c->tw_zh, nz / 2);
+  }
+  if (e) { return RF_ERR_CUDA; }
+  RF_CUDA(cudaMalloc(&c->zs_dev, nz * c->esize));
+  RF_CUDA(cudaMalloc(&c->da_dev, nz * c->esize));
+  RF_CUDA(cudaMalloc(&c->db_dev, nz * c->esize));
+  *out = c;
+  return RF_OK;
+}
+
+extern "C" int rf_destroy(rf_ctx* c) {
+  if (!c) return RF_OK;
+  cudaStreamSynchronize(c->stream);
+  void* ptrs[] = {c->field, c->recv, c->partials, c->stats_dev, c->tw_x, c->tw_y, c->tw_z,
+                  c->tw_zh, c->knots, c->lut, c->noise, c->zs_dev, c->da_dev, c->db_dev};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  delete c;
+  return RF_OK;
+}
+
+extern "C" int rf_set_stream(rf_ctx* c, void* s) {
+  if (!c) return fail(RF_ERR_ARG, "null ctx");
+  c->stream = s ? (cudaStream_t)s : c->own_stream;
+  return RF_OK;
+}
+extern "C" int rf_sync(rf_ctx* c) {
+  if (!c) return fail(RF_ERR_ARG, "null ctx");
+  RF_CUDA(cudaStreamSynchronize(c->stream));
+  return RF_OK;
+}
+extern "C" void* rf_host_alloc(long long bytes) {
+  void* p = nullptr;
+  if (bytes <= 0) return nullptr;
+  if (cudaHostAlloc(&p, (size_t)bytes, cudaHostAllocDefault) != cudaSuccess) {
+    g_err = "rf_host_alloc: cudaHostAlloc failed";
+    return nullptr;
+  }
+  return p;
+}
+extern "C" void rf_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+extern "C" int rf_is_fast(rf_ctx* c) { return c && c->fast ? 1 : 0; }
+extern "C" long long rf_launch_count(rf_ctx* c) { return c ? c->launches : 0; }
+extern "C" long long rf_field_elems(rf_ctx* c) {
+  return c ? (long long)c->nxl * c->ny * c->nz : 0;
+}
+extern "C" void* rf_device_ptr(rf_ctx* c, int which) {
+  if (!c) return nullptr;
+  switch (which) {
+    case RF_BUF_FIELD: return c->field;
+    case RF_BUF_RECV: return c->recv;
+    case RF_BUF_PARTIALS: return c->partials;
+  }
+  return nullptr;
+}
+extern "C" long long rf_buffer_bytes(rf_ctx* c, int which) {
+  if (!c) return 0;
+  switch (which) {
+    case RF_BUF_FIELD: return (long long)c->buf_bytes;
+    case RF_BUF_RECV: return c->recv ? (long long)c->buf_bytes : 0;
+    case RF_BUF_PARTIALS: return c->nparts * 2 * (long long)sizeof(double);
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// sigma table
+// ------------------------------------------------------------------------------------------
+static int cell_of(float v) {
+  int32_t b;
+  memcpy(&b, &v, 4);
+  return b >> 19;
+}
+static int cell_of(double v) {
+  int64_t b;
+  memcpy(&b, &v, 8);
+  return (int)(b >> 48);
+}
+static float cell_floor(int cell, float) {
+  int32_t b = cell << 19;
+  float v;
+  memcpy(&v, &b, 4);
+  return v;
+}
+static double cell_floor(int cell, double) {
+  int64_t b = (int64_t)cell << 48;
+  double v;
+  memcpy(&v, &b, 8);
+  return v;
+}
+
+template <typename T>
+static int build_table(rf_ctx* c, int n, const double* k, const double* sigma) {
+  const double N3 = (double)c->nx * c->ny * c->nz;
+  std::vector<knot<T>> kn(n);
+  std::vector<double> l2(n), sg(n);
+  for (int j = 0; j < n; ++j) {
+    kn[j].ksq = (T)(k[j] * k[j]);
+    l2[j] = 2.0 * std::log2(k[j]);
+    sg[j] = sigma[j] / N3;
+  }
+  for (int j = 0; j < n; ++j) {
+    kn[j].l2 = (T)l2[j];
+    kn[j].sig = (T)sg[j];
+    kn[j].slope = (j + 1 < n) ? (T)((sg[j + 1] - sg[j]) / (l2[j + 1] - l2[j])) : (T)0;
+    if (j > 0 && !(kn[j].ksq > kn[j - 1].ksq))
+      return fail(RF_ERR_ARG, "Power spectrum k values are not strictly increasing.");
+  }
+  const int base = cell_of(kn[0].ksq) - 1;
+  const int ln = cell_of(kn[n - 1].ksq) - base + 1;
+  if (ln <= 0 || ln > (1 << 20)) return fail(RF_ERR_ARG, "rf_set_power: bad k range");
+  std::vector<int16_t> lut(ln);
+  int cnt = 0;
+  for (int e = 0; e < ln; ++e) {
+    T edge = cell_floor(base + e, (T)0);
+    while (cnt < n && kn[cnt].ksq <= edge) ++cnt;
+    lut[e] = (int16_t)(cnt - 1);
+  }
+  if (c->knots) cudaFree(c->knots);
+  if (c->lut) cudaFree(c->lut);
+  c->knots = nullptr; c->lut = nullptr;
+  RF_CUDA(cudaMalloc(&c->knots, sizeof(knot<T>) * n));
+  RF_CUDA(cudaMalloc((void**)&c->lut, sizeof(int16_t) * ln));
+  // the table may be replaced while earlier work is still queued on the stream
+  RF_CUDA(cudaStreamSynchronize(c->stream));
+  RF_CUDA(cudaMemcpy(c->knots, kn.data(), sizeof(knot<T>) * n, cudaMemcpyHostToDevice));
+  RF_CUDA(cudaMemcpy(c->lut, lut.data(), sizeof(int16_t) * ln, cudaMemcpyHostToDevice));
+  c->ntab = n; c->lut_n = ln; c->lut_base = base;
+  return RF_OK;
+}
+
+extern "C" int rf_set_power(rf_ctx* c, int n, const double* k, const double* sigma, double spacing) {
+  if (!c || !k || !sigma) return fail(RF_ERR_ARG, "rf_set_power: null argument");
+  if (n < 2 || n > 32000) return fail(RF_ERR_ARG, "rf_set_power: need 2 <= n <= 32000 knots");
+  if (!(spacing > 0)) return fail(RF_ERR_ARG, "rf_set_power: spacing must be > 0");
+  for (int j = 0; j < n; ++j) {
+    if (!std::isfinite(k[j]) || !(k[j] > 0)) return fail(RF_ERR_ARG, "Power spectrum min(k) is <= 0.");
+    if (!std::isfinite(sigma[j]) || sigma[j] < 0)
+      return fail(RF_ERR_ARG, "Power values P(k) are not all non-negative.");
+  }
+  c->spacing = spacing;
+  int e = c->dtype == RF_F32 ? build_table<float>(c, n, k, sigma) : build_table<double>(c, n, k, sigma);
+  c->have_power = (e == RF_OK);
+  return e;
+}
+
+extern "C" int rf_set_noise(rf_ctx* c, const double* host_noise) {
+  if (!c) return fail(RF_ERR_ARG, "null ctx");
+  if (c->world > 1 && host_noise) return fail(RF_ERR_ARG, "rf_set_noise: single-GPU only");
+  RF_CUDA(cudaStreamSynchronize(c->stream));
+  if (!host_noise) {
+    if (c->noise) cudaFree(c->noise);
+    c->noise = nullptr;
+    return RF_OK;
+  }
+  const size_t n = (size_t)2 * c->nx * c->ny * (c->nz / 2 + 1);
+  if (!c->noise) RF_CUDA(cudaMalloc((void**)&c->noise, n * sizeof(double)));
+  RF_CUDA(cudaMemcpy(c->noise, host_noise, n * sizeof(double), cudaMemcpyHostToDevice));
+  return RF_OK;
+}
+
+template <typename T>
+static ModeGeom<T> make_geom(rf_ctx* c, uint64_t seed, int potential) {
+  ModeGeom<T> g;
+  g.nx = c->nx; g.ny = c->ny; g.nz = c->nz;
+  const double two_pi = 6.283185307179586476925286766559;
+  auto k0sq = [&](int n) {
+    double k0 = two_pi / ((double)n * c->spacing);
+    return (T)(k0 * k0);
+  };
+  g.k0x2 = k0sq(c->nx); g.k0y2 = k0sq(c->ny); g.k0z2 = k0sq(c->nz);
+  g.key0 = (uint32_t)seed; g.key1 = (uint32_t)(seed >> 32);
+  g.noise = c->noise;
+  g.potential = potential;
+  return g;
+}
+template <typename T>
+static SigmaTable<T> make_tab(rf_ctx* c) {
+  SigmaTable<T> t;
+  t.knots = (const knot<T>*)c->knots; t.lut = c->lut;
+  t.n = c->ntab; t.lut_n = c->lut_n; t.lut_base = c->lut_base;
+  return t;
+}
+
+static int ensure_partials(rf_ctx* c, long long n) {
+  if (n > c->parts_cap) {
+    if (c->partials) cudaFree(c->partials);
+    c->partials = nullptr;
+    RF_CUDA(cudaMalloc((void**)&c->partials, sizeof(double) * 2 * n));
+    c->parts_cap = n;
+  }
+  c->nparts = n;
+  return RF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// dispatch over the compiled tile-kernel sizes
+// ------------------------------------------------------------------------------------------
+#define RF_DISPATCH_N(N_, ...)                          \
+  switch (N_) {                                         \
+    case 64: { constexpr int NN = 64; __VA_ARGS__; } break;    \
+    case 128: { constexpr int NN = 128; __VA_ARGS__; } break;  \
+    case 256: { constexpr int NN = 256; __VA_ARGS__; } break;  \
+    case 512: { constexpr int NN = 512; __VA_ARGS__; } break;  \
+    case 1024: { constexpr int NN = 1024; __VA_ARGS__; } break;\
+    case 2048: { constexpr int NN = 2048; __VA_ARGS__; } break;\
+    case 4096: { constexpr int NN = 4096; __VA_ARGS__; } break;\
+    default: return fail(RF_ERR_ARG, "size not compiled");\
+  }
+
+template <typename T>
+static int run_generic_axis(rf_ctx* c, const void* in, void* out, int mode, int inverse, int n,
+                            long long na, long long nb, long long sa_in, long long sb_in,
+                            long long sa_out, long long sb_out, long long st_in, long long st_out,
+                            T scale, cudaStream_t s) {
+  LineSet ls;
+  ls.na = na; ls.nb = nb; ls.sa_in = sa_in; ls.sb_in = sb_in; ls.sa_out = sa_out; ls.sb_out = sb_out;
+  ls.stride_in = st_in; ls.stride_out = st_out; ls.n = n;
+  size_t smem = (size_t)3 * n * sizeof(cpx<T>);
+  if (smem > 220 * 1024) return fail(RF_ERR_ARG, "generic FFT: axis too long");
+  if (smem > 48 * 1024)
+    RF_CUDA(cudaFuncSetAttribute(generic_line_fft_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  long long lines = na * nb;
+  int grid = (int)std::min<long long>(lines, 148LL * 8);
+  int nt = n >= 512 ? 256 : (n >= 128 ? 128 : 64);
+  generic_line_fft_kernel<T><<<grid, nt, smem, s>>>(in, out, ls, mode, inverse, scale);
+  if (c) c->launches++;
+  RF_CUDA(cudaGetLastError());
+  return RF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// pass 1
+// ------------------------------------------------------------------------------------------
+template <typename T>
+static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
+  ModeGeom<T> g = make_geom<T>(c, seed, potential);
+  SigmaTable<T> tab = make_tab<T>(c);
+  c->field_is_real = false;
+  c->stats_valid = false;
+  if (c->fast) {
+    K1Params<T> p;
+    p.geom = g; p.tab = tab; p.out = (cpx<T>*)c->field; p.tw = (const cpx<T>*)c->tw_x;
+    p.ny_local = c->nyl; p.y0 = c->rank * c->nyl;
+    int e = 0;
+    RF_DISPATCH_N(c->nx, {
+      int grid = c->nyl * ((c->nz / 2) / FftPlan<T, NN>::TZ);
+      e = Launch<T, NN>::k1(c->noise != nullptr, p, grid, c->stream);
+    });
+    c->launches++;
+    RF_CUDA(e);
+    return RF_OK;
+  }
+  // generic path: public-layout k-space, internal normalisation, then the x lines
+  const int nzh = c->nz / 2 + 1;
+  const long long total = (long long)c->nx * c->ny * nzh;
+  int grid = (int)std::min<long long>((total + 255) / 256, 148LL * 16);
+  gen_kspace_public_kernel<T><<<grid, 256, 0, c->stream>>>(g, tab, (cpx<T>*)c->field, nullptr, (T)1, 0, c->ny);
+  c->launches++;
+  RF_CUDA(cudaGetLastError());
+  return run_generic_axis<T>(c, c->field, c->field, 0, 1, c->nx, c->ny, nzh, nzh, 1, nzh, 1,
+                             (long long)c->ny * nzh, (long long)c->ny * nzh, (T)1, c->stream);
+}
+
+extern "C" int rf_generate_xpass(rf_ctx* c, uint64_t seed, int potential) {
+  if (!c) return fail(RF_ERR_ARG, "null ctx");
+  if (!c->have_power) return fail(RF_ERR_STATE, "rf_generate_xpass: call rf_set_power first");
+  return c->dtype == RF_F32 ? xpass_impl<float>(c, seed, potential) : xpass_impl<double>(c, seed, potential);
+}
+
+// ------------------------------------------------------------------------------------------
+// passes 2 + 3
+// ------------------------------------------------------------------------------------------
+template <typename T>
+static int upload_table(rf_ctx* c, void* dst, const double* src, int n) {
+  std::vector<T> h(n);
+  for (int i = 0; i < n; ++i) h[i] = (T)src[i];
+  // pageable source: the copy is staged before the call returns, ordered on the stream
+  RF_CUDA(cudaMemcpyAsync(dst, h.data(), sizeof(T) * n, cudaMemcpyHostToDevice, c->stream));
+  RF_CUDA(cudaStreamSynchronize(c->stream));
+  return RF_OK;
+}
+
+template <typename T>
+static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
+  if (c->field_is_real) return fail(RF_ERR_STATE, "rf_finish_yz: no k-space block pending");
+  const T* zs = nullptr;
+  if (zscale) {
+    int e = upload_table<T>(c, c->zs_dev, zscale, c->nz);
+    if (e) return e;
+    zs = (const T*)c->zs_dev;
+  }
+  if (c->fast) {
+    const int nzc = c->nz / 2;
+    K2Params<T> p2;
+    p2.tw = (const cpx<T>*)c->tw_y;
+    p2.ncols = nzc;
+    p2.scale = (T)1;
+    p2.out = (cpx<T>*)c->field;
+    p2.out_outer = (long long)c->ny * nzc;
+    p2.out_row = nzc;
+    if (c->world > 1) {
+      p2.in = (const cpx<T>*)c->recv;
+      p2.in_outer = (long long)c->nyl * nzc;
+      p2.in_row = nzc;
+      p2.in_src = (long long)c->nxl * c->nyl * nzc;
+      p2.rows_per_src = c->nyl;
+    } else {
+      p2.in = (const cpx<T>*)c->field;
+      p2.in_outer = (long long)c->ny * nzc;
+      p2.in_row = nzc;
+      p2.in_src = 0;
+      p2.rows_per_src = c->ny;
+    }
+    int e = 0;
+    RF_DISPATCH_N(c->ny, {
+      int grid = c->nxl * (nzc / FftPlan<T, NN>::TZ);
+      e = Launch<T, NN>::k2(true, p2, grid, c->stream);
+    });
+    c->launches++;
+    RF_CUDA(e);
+    K3Params<T> p3;
+    p3.buf = (T*)c->field;
+    p3.nlines = (long long)c->nxl * c->ny;
+    p3.twH = (const cpx<T>*)c->tw_zh;
+    p3.twN = (const cpx<T>*)c->tw_z;
+    p3.zscale = zs;
+    p3.partials = nullptr;
+    RF_DISPATCH_N(c->nz, {
+      int tl = Launch<T, NN>::k3_lines_per_cta();
+      long long grid = (p3.nlines + tl - 1) / tl;
+      if (want_stats) {
+        int e2 = ensure_partials(c, grid);
+        if (e2) return e2;
+        p3.partials = c->partials;
+      }
+      e = Launch<T, NN>::k3(p3, (int)grid, c->stream);
+    });
+    c->launches++;
+    RF_CUDA(e);
+  } else {
+    const int nzh = c->nz / 2 + 1;
+    const long long plane = (long long)c->ny * nzh;
+    int e = run_generic_axis<T>(c, c->field, c->field, 0, 1, c->ny, c->nx, nzh, plane, 1, plane, 1,
+                                nzh, nzh, (T)1, c->stream);
+    if (e) return e;
+    if (!c->recv) RF_CUDA(cudaMalloc(&c->recv, c->buf_bytes));
+    // c2r out of place: complex pitch nzh -> dense real pitch nz
+    e = run_generic_axis<T>(c, c->field, c->recv, 1, 1, c->nz, (long long)c->nx * c->ny, 1, nzh, 0,
+                            c->nz, 0, 1, 1, (T)1, c->stream);
+    if (e) return e;
+    std::swap(c->field, c->recv);
+    const long long n = (long long)c->nx * c->ny * c->nz;
+    if (want_stats) {
+      int e2 = ensure_partials(c, 1024);
+      if (e2) return e2;
+      stats_partial_kernel<T><<<1024, 256, 0, c->stream>>>((const T*)c->field, n, c->partials);
+      c->launches++;
+    }
+  }
+  if (want_stats) {
+    stats_final_kernel<<<1, 256, 0, c->stream>>>(c->partials, c->nparts, c->stats_dev);
+    c->launches++;
+    RF_CUDA(cudaGetLastError());
+    c->stats_valid = true;
+  }
+  c->field_is_real = true;
+  return RF_OK;
+}
+
+// out = field * zs[z], used by the generic path for the light-cone factor
+template <typename T>
+__global__ void scale_z_kernel(T* field, long long n, int nz, const T* zs) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x)
+    field[i] *= __ldg(zs + (int)(i % nz));
+}
+
+template <typename T>
+static int finish_generic_with_scale(rf_ctx* c, const double* zscale, int want_stats) {
+  int e = finish_impl<T>(c, nullptr, want_stats);
+  if (e) return e;
+  e = upload_table<T>(c, c->zs_dev, zscale, c->nz);
+  if (e) return e;
+  const long long n = (long long)c->nx * c->ny * c->nz;
+  int grid = (int)std::min<long long>((n + 255) / 256, 148LL * 16);
+  scale_z_kernel<T><<<grid, 256, 0, c->stream>>>((T*)c->field, n, c->nz, (const T*)c->zs_dev);
+  c->launches++;
+  RF_CUDA(cudaGetLastError());
+  return RF_OK;
+}
+
+extern "C" int rf_finish_yz(rf_ctx* c, const double* zscale, int want_stats) {
+  if (!c) return fail(RF_ERR_ARG, "null ctx");
+  if (!c->fast && zscale)
+    return c->dtype == RF_F32 ? finish_generic_with_scale<float>(c, zscale, want_stats)
+                              : finish_generic_with_scale<double>(c, zscale, want_stats);
+  return c->dtype == RF_F32 ? finish_impl<float>(c, zscale, want_stats)
+                            : finish_impl<double>(c, zscale, want_stats);
+}
+
+extern "C" int rf_generate_delta(rf_ctx* c, uint64_t seed, int potential, const double* zscale,
+                                 int want_stats) {
+  if (!c) return fail(RF_ERR_ARG, "null ctx");
+  if (c->world != 1) return fail(RF_ERR_STATE, "rf_generate_delta: single-GPU only; use xpass/finish");
+  int e = rf_generate_xpass(c, seed, potential);
+  if (e) return e;
+  return rf_finish_yz(c, zscale, want_stats);
+}
+
+extern "C" int rf_stats(rf_ctx* c, double* sum, double* sumsq, long long* count) {
+  if (!c) return fail(RF_ERR_ARG, "null ctx");
+  if (!c->stats_valid) return fail(RF_ERR_STATE, "rf_stats: no statistics were accumulated");
+  double h[2];
+  RF_CUDA(cudaMemcpyAsync(h, c->stats_dev, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+  RF_CUDA(cudaStreamSynchronize(c->stream));
+  if (sum) *sum = h[0];
+  if (sumsq) *sumsq = h[1];
+  if (count) *count = rf_field_elems(c);
+  return RF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// density epilogue
+// ------------------------------------------------------------------------------------------
+template <typename T>
+static int density_impl(rf_ctx* c, int lognormal, double sigma, const double* growth, const double* rho) {
+  std::vector<double> a(c->nz), b(c->nz);
+  for (int z = 0; z < c->nz; ++z) {
+    if (lognormal) {
+      double t = 1.0 + (sigma * growth[z]) * (sigma * growth[z]);
+      a[z] = std::sqrt(std::log(t)) / sigma;
+      b[z] = rho[z] / std::sqrt(t);
+    } else {
+      a[z] = growth[z];
+      b[z] = rho[z];
+    }
+  }
+  int e = upload_table<T>(c, c->da_dev, a.data(), c->nz);
+  if (e) return e;
+  e = upload_table<T>(c, c->db_dev, b.data(), c->nz);
+  if (e) return e;
+  const long long n = rf_field_elems(c);
+  if (c->nz % 4 == 0) {
+    const long long n4 = n / 4;
+    int grid = (int)std::min<long long>((n4 + 255) / 256, 148LL * 32);
+    density_kernel_v4<T><<<grid, 256, 0, c->stream>>>((T*)c->field, n4, c->nz, (const T*)c->da_dev,
+                                                      (const T*)c->db_dev, lognormal);
+  } else {
+    int grid = (int)std::min<long long>((n + 255) / 256, 148LL * 32);
+    density_kernel<T><<<grid, 256, 0, c->stream>>>((T*)c->field, n, c->nz, (const T*)c->da_dev,
+                                                   (const T*)c->db_dev, lognormal);
+  }
+  c->launches++;
+  RF_CUDA(cudaGetLastError());
+  return RF_OK;
+}
+
+extern "C" int rf_density(rf_ctx* c, int lognormal, double sigma, const double* growth, const double* rho) {
+  if (!c || !growth || !rho) return fail(RF_ERR_ARG, "rf_density: null argument");
+  if (!c->field_is_real) return fail(RF_ERR_STATE, "rf_density: no real-space field");
+  if (lognormal && !(sigma > 0)) return fail(RF_ERR_ARG, "rf_density: sigma must be > 0");
+  return c->dtype == RF_F32 ? density_impl<float>(c, lognormal, sigma, growth, rho)
+                            : density_impl<double>(c, lognormal, sigma, growth, rho);
+}
+
+extern "C" int rf_copy_field(rf_ctx* c, void* host_dst) {
+  if (!c || !host_dst) return fail(RF_ERR_ARG, "rf_copy_field: null argument");
+  if (!c->field_is_real) return fail(RF_ERR_STATE, "rf_copy_field: no real-space field");
+  RF_CUDA(cudaMemcpyAsync(host_dst, c->field, (size_t)rf_field_elems(c) * c->esize,
+                          cudaMemcpyDeviceToHost, c->stream));
+  RF_CUDA(cudaStreamSynchronize(c->stream));
+  return RF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// stage-level k-space export
+// ------------------------------------------------------------------------------------------
+template <typename T>
+static int kspace_impl(rf_ctx* c, uint64_t seed, int potential, void* host, int32_t* host_bins) {
+  ModeGeom<T> g = make_geom<T>(c, seed, potential);
+  SigmaTable<T> tab = make_tab<T>(c);
+  const int nzh = c->nz / 2 + 1;
+  const long long total = (long long)c->nx * c->nyl * nzh;
+  int32_t* dbins = nullptr;
+  if (host_bins) RF_CUDA(cudaMalloc((void**)&dbins, sizeof(int32_t) * total));
+  const double N3 = (double)c->nx * c->ny * c->nz;
+  int grid = (int)std::min<long long>((total + 255) / 256, 148LL * 16);
+  gen_kspace_public_kernel<T><<<grid, 256, 0, c->stream>>>(g, tab, (cpx<T>*)c->field, dbins, (T)N3,
+                                                           c->rank * c->nyl, c->nyl);
+  c->launches++;
+  c->field_is_real = false;
+  c->stats_valid = false;
+  RF_CUDA(cudaGetLastError());
+  RF_CUDA(cudaMemcpyAsync(host, c->field, sizeof(cpx<T>) * total, cudaMemcpyDeviceToHost, c->stream));
+  if (host_bins)
+    RF_CUDA(cudaMemcpyAsync(host_bins, dbins, sizeof(int32_t) * total, cudaMemcpyDeviceToHost, c->stream));
+  RF_CUDA(cudaStreamSynchronize(c->stream));
+  if (dbins) cudaFree(dbins);
+  return RF_OK;
+}
+
+extern "C" int rf_kspace_public(rf_ctx* c, uint64_t seed, int potential, void* host_cplx, int32_t* host_bins) {
+  if (!c || !host_cplx) return fail(RF_ERR_ARG, "rf_kspace_public: null argument");
+  if (!c->have_power) return fail(RF_ERR_STATE, "rf_kspace_public: call rf_set_power first");
+  return c->dtype == RF_F32 ? kspace_impl<float>(c, seed, potential, host_cplx, host_bins)
+                            : kspace_impl<double>(c, seed, potential, host_cplx, host_bins);
+}
+
+// ------------------------------------------------------------------------------------------
+// transform.Plan.execute on host arrays
+// ------------------------------------------------------------------------------------------
+template <typename T>
+static int plan_impl(int nx, int ny, int nz, int inverse, int packed, const void* hin, void* hout) {
+  const long long nzh = nz / 2 + 1;
+  const long long ncplx = packed ? (long long)nx * ny * nzh : (long long)nx * ny * nz;
+  const long long nreal = (long long)nx * ny * nz;
+  const size_t cbytes = sizeof(cpx<T>) * ncplx, rbytes = sizeof(T) * nreal;
+  void *a = nullptr, *b = nullptr;
+  RF_CUDA(cudaMalloc(&a, cbytes));
+  cudaStream_t s = nullptr;
+  const double N3 = (double)nx * ny * nz;
+  int e = RF_OK;
+  auto cleanup = [&]() { if (a) cudaFree(a); if (b) cudaFree(b); };
+#define PL_CUDA(x) do { cudaError_t e__ = (cudaError_t)(x); if (e__ != cudaSuccess) { cleanup(); return fail(RF_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e__)); } } while (0)
+#define PL_RUN(x) do { e = (x); if (e) { cleanup(); return e; } } while (0)
+  if (!packed) {
+    PL_CUDA(cudaMemcpy(a, hin, cbytes, cudaMemcpyHostToDevice));
+    const long long plane = (long long)ny * nz;
+    PL_RUN(run_generic_axis<T>(nullptr, a, a, 0, inverse, nx, ny, nz, nz, 1, nz, 1, plane, plane, (T)1, s));
+    PL_RUN(run_generic_axis<T>(nullptr, a, a, 0, inverse, ny, nx, nz, plane, 1, plane, 1, nz, nz, (T)1, s));
+    PL_RUN(run_generic_axis<T>(nullptr, a, a, 0, inverse, nz, (long long)nx * ny, 1, nz, 0, nz, 0, 1, 1,
+                               inverse ? (T)(1.0 / N3) : (T)1, s));
+    PL_CUDA(cudaMemcpy(hout, a, cbytes, cudaMemcpyDeviceToHost));
+  } else if (inverse) {
+    PL_CUDA(cudaMalloc(&b, rbytes));
+    PL_CUDA(cudaMemcpy(a, hin, cbytes, cudaMemcpyHostToDevice));
+    const long long plane = (long long)ny * nzh;
+    PL_RUN(run_generic_axis<T>(nullptr, a, a, 0, 1, nx, ny, nzh, nzh, 1, nzh, 1, plane, plane, (T)1, s));
+    PL_RUN(run_generic_axis<T>(nullptr, a, a, 0, 1, ny, nx, nzh, plane, 1, plane, 1, nzh, nzh, (T)1, s));
+    PL_RUN(run_generic_axis<T>(nullptr, a, b, 1, 1, nz, (long long)nx * ny, 1, nzh, 0, nz, 0, 1, 1,
+                               (T)(1.0 / N3), s));
+    PL_CUDA(cudaMemcpy(hout, b, rbytes, cudaMemcpyDeviceToHost));
+  } else {
+    PL_CUDA(cudaMalloc(&b, rbytes));
+    PL_CUDA(cudaMemcpy(b, hin, rbytes, cudaMemcpyHostToDevice));
+    const long long plane = (long long)ny * nzh;
+    PL_RUN(run_generic_axis<T>(nullptr, b, a, 2, 0, nz, (long long)nx * ny, 1, nz, 0, nzh, 0, 1, 1, (T)1, s));
+    PL_RUN(run_generic_axis<T>(nullptr, a, a, 0, 0, ny, nx, nzh, plane, 1, plane, 1, nzh, nzh, (T)1, s));
+    PL_RUN(run_generic_axis<T>(nullptr, a, a, 0, 0, nx, ny, nzh, nzh, 1, nzh, 1, plane, plane, (T)1, s));
+    PL_CUDA(cudaMemcpy(hout, a, cbytes, cudaMemcpyDeviceToHost));
+  }
+  cleanup();
+  return RF_OK;
+#undef PL_CUDA
+#undef PL_RUN
+}
+
+extern "C" int rf_plan_execute(int nx, int ny, int nz, int dtype, int inverse, int packed,
+                               const void* host_in, void* host_out) {
+  if (!host_in || !host_out) return fail(RF_ERR_ARG, "rf_plan_execute: null argument");
+  if (nx <= 0 || ny <= 0 || nz <= 0 || (nx % 2) || (ny % 2) || (nz % 2))
+    return fail(RF_ERR_ARG, "All shape dimensions must be even.");
+  return dtype == RF_F32 ? plan_impl<float>(nx, ny, nz, inverse, packed, host_in, host_out)
+                         : plan_impl<double>(nx, ny, nz, inverse, packed, host_in, host_out);
+}
+
+// ------------------------------------------------------------------------------------------
+// stage functions on host arrays
+// ------------------------------------------------------------------------------------------
+template <class F>
+static int with_device_copy(void* host, size_t bytes, F&& body) {
+  void* d = nullptr;
+  RF_CUDA(cudaMalloc(&d, bytes));
+  cudaError_t e = cudaMemcpy(d, host, bytes, cudaMemcpyHostToDevice);
+  int r = RF_OK;
+  if (e == cudaSuccess) r = body(d);
+  if (e == cudaSuccess && r == RF_OK) e = cudaMemcpy(host, d, bytes, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) return fail(RF_ERR_CUDA, cudaGetErrorString(e));
+  return r;
+}
+static int grid_for(long long n) { return (int)std::min<long long>((n + 255) / 256, 148LL * 16); }
+
+extern "C" int rf_stage_fill_log10k(int nx, int ny, int nz, int packed, int dtype, double spacing,
+                                    void* host) {
+  if (!host) return fail(RF_ERR_ARG, "null argument");
+  const int ncols = packed ? nz / 2 + 1 : nz;
+  const long long total = (long long)nx * ny * ncols;
+  const double lambda0 = spacing / 6.283185307179586476925286766559;
+  const size_t es = dtype == RF_F32 ? 8 : 16;
+  return with_device_copy(host, es * total, [&](void* d) {
+    if (dtype == RF_F32)
+      stage_fill_log10k_kernel<float><<<grid_for(total), 256>>>((cpx<float>*)d, nx, ny, nz, ncols, lambda0);
+    else
+      stage_fill_log10k_kernel<double><<<grid_for(total), 256>>>((cpx<double>*)d, nx, ny, nz, ncols, lambda0);
+    RF_CUDA(cudaGetLastError());
+    return (int)RF_OK;
+  });
+}
+
+extern "C" int rf_stage_tabulate(long long nelem, int dtype, int n, const double* log10k,
+                                 const double* sigma, void* host) {
+  if (!host || !log10k || !sigma || n < 2) return fail(RF_ERR_ARG, "bad argument");
+  double *dx = nullptr, *df = nullptr;
+  RF_CUDA(cudaMalloc((void**)&dx, sizeof(double) * n));
+  RF_CUDA(cudaMalloc((void**)&df, sizeof(double) * n));
+  cudaMemcpy(dx, log10k, sizeof(double) * n, cudaMemcpyHostToDevice);
+  cudaMemcpy(df, sigma, sizeof(double) * n, cudaMemcpyHostToDevice);
+  const size_t es = dtype == RF_F32 ? 8 : 16;
+  int r = with_device_copy(host, es * nelem, [&](void* d) {
+    if (dtype == RF_F32)
+      stage_tabulate_kernel<float><<<grid_for(nelem), 256>>>((cpx<float>*)d, nelem, n, dx, df);
+    else
+      stage_tabulate_kernel<double><<<grid_for(nelem), 256>>>((cpx<double>*)d, nelem, n, dx, df);
+    RF_CUDA(cudaGetLastError());
+    return (int)RF_OK;
+  });
+  cudaFree(dx);
+  cudaFree(df);
+  return r;
+}
+
+extern "C" int rf_stage_randomize(long long nelem, int dtype, uint64_t seed, void* host) {
+  if (!host) return fail(RF_ERR_ARG, "null argument");
+  const size_t es = dtype == RF_F32 ? 8 : 16;
+  return with_device_copy(host, es * nelem, [&](void* d) {
+    if (dtype == RF_F32)
+      stage_randomize_kernel<float><<<grid_for(nelem), 256>>>((cpx<float>*)d, nelem, (uint32_t)seed, (uint32_t)(seed >> 32));
+    else
+      stage_randomize_kernel<double><<<grid_for(nelem), 256>>>((cpx<double>*)d, nelem, (uint32_t)seed, (uint32_t)(seed >> 32));
+    RF_CUDA(cudaGetLastError());
+    return (int)RF_OK;
+  });
+}
+
+extern "C" int rf_stage_symmetrize(int nx, int ny, int nz, int packed, int dtype, void* host) {
+  if (!host) return fail(RF_ERR_ARG, "null argument");
+  if ((nx % 2) || (ny % 2) || (nz % 2)) return fail(RF_ERR_ARG, "All shape dimensions must be even.");
+  const int ncols = packed ? nz / 2 + 1 : nz;
+  const long long total = (long long)nx * ny * ncols;
+  const size_t es = dtype == RF_F32 ? 8 : 16;
+  void* src = nullptr;
+  RF_CUDA(cudaMalloc(&src, es * total));
+  cudaMemcpy(src, host, es * total, cudaMemcpyHostToDevice);
+  int r = with_device_copy(host, es * total, [&](void* d) {
+    if (dtype == RF_F32)
+      stage_symmetrize_kernel<float><<<grid_for(total), 256>>>((const cpx<float>*)src, (cpx<float>*)d, nx, ny, nz, packed);
+    else
+      stage_symmetrize_kernel<double><<<grid_for(total), 256>>>((const cpx<double>*)src, (cpx<double>*)d, nx, ny, nz, packed);
+    RF_CUDA(cudaGetLastError());
+    return (int)RF_OK;
+  });
+  cudaFree(src);
+  return r;
+}

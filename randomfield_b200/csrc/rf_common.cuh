@@ -1,0 +1,326 @@
+// rf_common.cuh -- shared device building blocks for the B200 field-synthesis path.
+//
+// Contents: complex type, compile-time loops, in-register radix-R DIF butterflies with
+// constant twiddles, Philox4x32-10, Box-Muller, the sigma(k) table lookup, and the
+// Hermitian pairing rule.  Everything here is header-only and used by both the fast
+// tile kernels (rf_fast.cuh) and the stage-level kernels (rf_generic.cu).
+//
+// Reference behaviour restated (never copied): randomfield/powertools.py:27-61,125-164
+// (k grid, sigma interpolation), randomfield/random.py:12-29 (sigma * normal deviates),
+// randomfield/transform.py:140-158 (packed Hermitian fix-up).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <type_traits>
+
+namespace rf {
+
+// ----------------------------------------------------------------------------------------
+// complex number, aligned so that float -> 8-byte and double -> 16-byte vector accesses
+// ----------------------------------------------------------------------------------------
+template <typename T>
+struct alignas(2 * sizeof(T)) cpx {
+  T x, y;
+};
+
+template <typename T>
+__host__ __device__ __forceinline__ cpx<T> operator+(cpx<T> a, cpx<T> b) {
+  return {a.x + b.x, a.y + b.y};
+}
+template <typename T>
+__host__ __device__ __forceinline__ cpx<T> operator-(cpx<T> a, cpx<T> b) {
+  return {a.x - b.x, a.y - b.y};
+}
+template <typename T>
+__host__ __device__ __forceinline__ cpx<T> cmul(cpx<T> a, cpx<T> b) {
+  return {a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x};
+}
+template <typename T>
+__host__ __device__ __forceinline__ cpx<T> cconj(cpx<T> a) {
+  return {a.x, -a.y};
+}
+
+// ----------------------------------------------------------------------------------------
+// compile-time loop: body receives std::integral_constant<int, I>
+// ----------------------------------------------------------------------------------------
+template <int B, int E, class F>
+__host__ __device__ __forceinline__ void sfor(F&& f) {
+  if constexpr (B < E) {
+    f(std::integral_constant<int, B>{});
+    sfor<B + 1, E>(f);
+  }
+}
+
+// ----------------------------------------------------------------------------------------
+// 32nd roots of unity as compile-time constants
+// ----------------------------------------------------------------------------------------
+__host__ __device__ constexpr double rf_c32(int k) {
+  // cos(2*pi*k/32) for k in [0, 8]
+  return k == 0   ? 1.0
+         : k == 1 ? 0.98078528040323044913
+         : k == 2 ? 0.92387953251128675613
+         : k == 3 ? 0.83146961230254523708
+         : k == 4 ? 0.70710678118654752440
+         : k == 5 ? 0.55557023301960222474
+         : k == 6 ? 0.38268343236508977173
+         : k == 7 ? 0.19509032201612826785
+                  : 0.0;
+}
+__host__ __device__ constexpr double rf_cos32(int k) {
+  k = ((k % 32) + 32) % 32;
+  if (k > 16) k = 32 - k;               // cos is even about 16
+  return (k > 8) ? -rf_c32(16 - k) : rf_c32(k);
+}
+__host__ __device__ constexpr double rf_sin32(int k) { return rf_cos32(k - 8); }
+
+// multiply by W32^IDX, where W = exp(+2*pi*i/32) for the inverse and exp(-...) forward.
+template <int IDX, bool INV, typename T>
+__device__ __forceinline__ cpx<T> mul_tw32(cpx<T> d) {
+  constexpr int k = ((IDX % 32) + 32) % 32;
+  if constexpr (k == 0) {
+    return d;
+  } else if constexpr (k == 16) {
+    return {-d.x, -d.y};
+  } else if constexpr (k == 8) {
+    if constexpr (INV) return {-d.y, d.x};
+    else return {d.y, -d.x};
+  } else if constexpr (k == 24) {
+    if constexpr (INV) return {d.y, -d.x};
+    else return {-d.y, d.x};
+  } else if constexpr (k == 4 || k == 12 || k == 20 || k == 28) {
+    constexpr T s = (T)0.70710678118654752440;
+    constexpr T cs = (k == 4 || k == 28) ? (T)1 : (T)-1;          // sign of cos
+    constexpr T sn0 = (k == 4 || k == 12) ? (T)1 : (T)-1;         // sign of sin(+)
+    constexpr T sn = INV ? sn0 : -sn0;
+    // (cs + i sn) * (x + i y) * s = (cs x - sn y) + i (cs y + sn x)
+    return {(cs * d.x - sn * d.y) * s, (cs * d.y + sn * d.x) * s};
+  } else {
+    constexpr T c = (T)rf_cos32(k);
+    constexpr T s = (T)(INV ? rf_sin32(k) : -rf_sin32(k));
+    return {d.x * c - d.y * s, d.x * s + d.y * c};
+  }
+}
+
+// ----------------------------------------------------------------------------------------
+// in-register radix-R decimation-in-frequency DFT, R in {2,4,8,16,32}.
+// Output k of the DFT ends up in v[brev<R>(k)].
+// ----------------------------------------------------------------------------------------
+template <int R>
+__host__ __device__ constexpr int brev(int k) {
+  int r = 0;
+  for (int b = 1; b < R; b <<= 1) {
+    r = (r << 1) | (k & 1);
+    k >>= 1;
+  }
+  return r;
+}
+
+template <int R, int HALF, bool INV, typename T>
+__device__ __forceinline__ void dif_stage(cpx<T> (&v)[R]) {
+  sfor<0, R / (2 * HALF)>([&](auto gi) {
+    constexpr int g = decltype(gi)::value * 2 * HALF;
+    sfor<0, HALF>([&](auto ki) {
+      constexpr int k = decltype(ki)::value;
+      cpx<T> a = v[g + k], b = v[g + k + HALF];
+      v[g + k] = a + b;
+      v[g + k + HALF] = mul_tw32<(k * 16) / HALF, INV>(a - b);
+    });
+  });
+  if constexpr (HALF > 1) dif_stage<R, HALF / 2, INV>(v);
+}
+
+template <int R, bool INV, typename T>
+__device__ __forceinline__ void fft_dif(cpx<T> (&v)[R]) {
+  static_assert(R == 1 || R == 2 || R == 4 || R == 8 || R == 16 || R == 32, "radix");
+  if constexpr (R > 1) dif_stage<R, R / 2, INV>(v);
+}
+
+// ----------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al. 2011).  Counter = 128 bit, key = 64 bit.
+// ----------------------------------------------------------------------------------------
+struct philox_out {
+  uint32_t w[4];
+};
+
+__host__ __device__ __forceinline__ philox_out philox4x32_10(uint32_t c0, uint32_t c1,
+                                                             uint32_t c2, uint32_t c3,
+                                                             uint32_t k0, uint32_t k1) {
+  constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+  constexpr uint32_t W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint64_t p0 = (uint64_t)M0 * c0;
+    uint64_t p1 = (uint64_t)M1 * c2;
+    uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+    uint32_t n1 = (uint32_t)p1;
+    uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+    uint32_t n3 = (uint32_t)p0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += W0; k1 += W1;
+  }
+  return {{c0, c1, c2, c3}};
+}
+
+// Box-Muller: two 32-bit words -> one complex standard-normal deviate (re, im each N(0,1)).
+// u1 = ((wa >> 9) + 0.5) / 2^23 in (0,1); angle = pi * (int32)wb / 2^31 in [-pi, pi).
+template <typename T>
+__device__ __forceinline__ cpx<T> box_muller(uint32_t wa, uint32_t wb);
+
+template <>
+__device__ __forceinline__ cpx<float> box_muller<float>(uint32_t wa, uint32_t wb) {
+  float u1 = __int_as_float(0x3f800000u | (wa >> 9)) + (-1.0f + 5.9604644775390625e-8f);
+  float l2 = __log2f(u1);                                   // MUFU.LG2
+  float r2 = l2 * -1.3862943611198906f;                     // -2 ln2 * log2(u1) = -2 ln(u1)
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(r2));
+  float ang = (float)(int32_t)wb * 1.4629180792671596e-9f;  // pi / 2^31
+  float s, c;
+  __sincosf(ang, &s, &c);
+  return {r * c, r * s};
+}
+
+template <>
+__device__ __forceinline__ cpx<double> box_muller<double>(uint32_t wa, uint32_t wb) {
+  double u1 = ((double)(wa >> 9) + 0.5) * (1.0 / 8388608.0);
+  double r = sqrt(-2.0 * log(u1));
+  double s, c;
+  sincospi((double)(int32_t)wb * (1.0 / 2147483648.0), &s, &c);
+  return {r * c, r * s};
+}
+
+// ----------------------------------------------------------------------------------------
+// sigma(k) table in device memory (built on the host by rf_set_power)
+// ----------------------------------------------------------------------------------------
+template <typename T>
+struct alignas(4 * sizeof(T)) knot {
+  T ksq;    // k_j^2 rounded to T (bin edges: bin j is ksq[j] <= k^2 < ksq[j+1])
+  T l2;     // log2(k_j^2) rounded to T
+  T sig;    // sigma_j (already divided by nx*ny*nz)
+  T slope;  // d sigma / d log2(k^2) on segment j
+};
+
+template <typename T>
+struct SigmaTable {
+  const knot<T>* knots;   // n entries
+  const int16_t* lut;     // lut_n entries: start bin for each coarse cell
+  int n;
+  int lut_n;
+  int lut_base;           // coarse-cell id of lut[0]
+};
+
+// coarse cell id: exponent + 4 mantissa bits of k^2 (16 cells per octave)
+__device__ __forceinline__ int coarse_cell(float v) { return __float_as_int(v) >> 19; }
+__device__ __forceinline__ int coarse_cell(double v) { return __double2hiint(v) >> 16; }
+__device__ __forceinline__ float rf_log2(float v) { return __log2f(v); }
+__device__ __forceinline__ double rf_log2(double v) { return log2(v); }
+
+// canonical bin index: largest j with knots[j].ksq <= ksq, or -1.
+template <typename T>
+__device__ __forceinline__ int sigma_bin(const SigmaTable<T>& tab, T ksq) {
+  int e = coarse_cell(ksq) - tab.lut_base;
+  e = max(0, min(e, tab.lut_n - 1));
+  int j = __ldg(tab.lut + e);
+  while (j + 1 < tab.n && __ldg(&tab.knots[j + 1].ksq) <= ksq) ++j;
+  return j;
+}
+
+template <typename T>
+__device__ __forceinline__ T sigma_eval(const SigmaTable<T>& tab, T ksq, int* bin_out = nullptr) {
+  int j = sigma_bin(tab, ksq);
+  if (bin_out) *bin_out = j;
+  int seg = min(j, tab.n - 2);
+  bool outside = (j < 0) || (j == tab.n - 1 && ksq > __ldg(&tab.knots[tab.n - 1].ksq));
+  seg = max(seg, 0);
+  const knot<T>* kp = tab.knots + seg;
+  T l2 = __ldg(&kp->l2), sg = __ldg(&kp->sig), sl = __ldg(&kp->slope);
+  T v = sg + sl * (rf_log2(ksq) - l2);
+  return outside ? (T)0 : v;
+}
+
+// ----------------------------------------------------------------------------------------
+// grid geometry + mode generation
+// ----------------------------------------------------------------------------------------
+template <typename T>
+struct ModeGeom {
+  int nx, ny, nz;          // full grid
+  T k0x2, k0y2, k0z2;      // (2*pi/(n*spacing))^2 per axis, rounded to T
+  uint32_t key0, key1;     // Philox key (seed)
+  const double* noise;     // injected white noise in reference order, or nullptr
+  int potential;           // 1: scale modes by 1/k^2 (Newtonian potential source)
+};
+
+// signed mode number squared as T (exact for n <= 8192)
+template <typename T>
+__device__ __forceinline__ T mode_sq(int i, int n) {
+  int j = (i <= n / 2) ? i : i - n;
+  return (T)(j * j);
+}
+
+// canonical k^2: fma(jx^2, k0x2, fma(jy^2, k0y2, jz^2 * k0z2)) with explicit rounding
+__device__ __forceinline__ float ksq_canon(float jx2, float jy2, float jz2, float a, float b, float c) {
+  return __fmaf_rn(jx2, a, __fmaf_rn(jy2, b, __fmul_rn(jz2, c)));
+}
+__device__ __forceinline__ double ksq_canon(double jx2, double jy2, double jz2, double a, double b, double c) {
+  return __fma_rn(jx2, a, __fma_rn(jy2, b, __dmul_rn(jz2, c)));
+}
+
+// Hermitian pairing on the planes iz in {0, nz/2} (public packed layout):
+// an element is a slave iff iy > ny/2, or iy in {0, ny/2} and ix > nx/2; its master is
+// ((nx-ix)%nx, (ny-iy)%ny, iz).   (transform.py:140-158, verified against it in tests.)
+struct Pairing {
+  int mx, my;
+  bool conj;
+  bool vertex;
+};
+__device__ __forceinline__ Pairing hermitian_pairing(int ix, int iy, int iz, int nx, int ny, int nz) {
+  Pairing p{ix, iy, false, false};
+  if (iz == 0 || iz == nz / 2) {
+    bool yedge = (iy == 0 || iy == ny / 2);
+    bool slave = (iy > ny / 2) || (yedge && ix > nx / 2);
+    if (slave) {
+      p.mx = (nx - ix) % nx;
+      p.my = (ny - iy) % ny;
+      p.conj = true;
+    }
+    p.vertex = yedge && (ix == 0 || ix == nx / 2);
+  }
+  return p;
+}
+
+// raw (unsymmetrised) mode: sigma(|k|) * complex normal deviate.
+// Philox counter: q = ((ix mod nx/2) * ny + iy) * (nz/2+1) + iz; words (0,1) serve
+// ix < nx/2 and words (2,3) serve ix >= nx/2.
+template <typename T>
+__device__ __forceinline__ cpx<T> raw_mode(const ModeGeom<T>& g, const SigmaTable<T>& tab,
+                                           int ix, int iy, int iz) {
+  T ksq = ksq_canon(mode_sq<T>(ix, g.nx), mode_sq<T>(iy, g.ny), mode_sq<T>(iz, g.nz),
+                    g.k0x2, g.k0y2, g.k0z2);
+  T sig = sigma_eval(tab, ksq);
+  if (g.potential) sig = (ksq > (T)0) ? sig / ksq : (T)0;
+  const int nzh = g.nz / 2 + 1;
+  if (g.noise) {
+    size_t idx = 2 * (((size_t)ix * g.ny + iy) * nzh + iz);
+    double nr = __ldg(g.noise + idx), ni = __ldg(g.noise + idx + 1);
+    return {(T)((double)sig * nr), (T)((double)sig * ni)};
+  }
+  const int hx = g.nx / 2;
+  int px = (ix >= hx) ? ix - hx : ix;
+  uint64_t q = ((uint64_t)px * g.ny + iy) * nzh + iz;
+  philox_out o = philox4x32_10((uint32_t)q, (uint32_t)(q >> 32), 0u, 0u, g.key0, g.key1);
+  cpx<T> n = (ix >= hx) ? box_muller<T>(o.w[2], o.w[3]) : box_muller<T>(o.w[0], o.w[1]);
+  return {sig * n.x, sig * n.y};
+}
+
+// symmetrised mode in the public (nx, ny, nz/2+1) layout
+template <typename T>
+__device__ __forceinline__ cpx<T> sym_mode(const ModeGeom<T>& g, const SigmaTable<T>& tab,
+                                           int ix, int iy, int iz) {
+  Pairing p = hermitian_pairing(ix, iy, iz, g.nx, g.ny, g.nz);
+  cpx<T> v = raw_mode(g, tab, p.mx, p.my, iz);
+  if (p.conj) v.y = -v.y;
+  if (p.vertex) v.y = (T)0;
+  if (ix == 0 && iy == 0 && iz == 0) v.x = (T)0;
+  return v;
+}
+
+}  // namespace rf
