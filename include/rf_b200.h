@@ -111,6 +111,12 @@ int rf_stage_tabulate(long long nelem, int dtype, int n, const double* log10k,
 int rf_stage_randomize(long long nelem, int dtype, uint64_t seed, void* host_cplx);
 int rf_stage_symmetrize(int nx, int ny, int nz, int packed, int dtype, void* host_cplx);
 
+/* cosmotools.apply_lognormal_transform (cosmotools.py:206-221) / the linear branch of
+ * convert_delta_to_density (generate.py:271-273) on a host real array whose last axis has
+ * nz entries; sigma <= 0 means "use np.std of the data" (computed on the device). */
+int rf_stage_density(long long nelem, int nz, int dtype, int lognormal, double sigma,
+                     const double* growth, const double* rho, void* host_real);
+
 /* page-locked host memory for result arrays (transform.allocate, transform.py:10-43, uses
  * SIMD-aligned memory for the same reason: fast transfers into the transform) */
 void* rf_host_alloc(long long bytes);

@@ -778,3 +778,52 @@ extern "C" int rf_stage_symmetrize(int nx, int ny, int nz, int packed, int dtype
   cudaFree(src);
   return r;
 }
+
+template <typename T>
+static int stage_density_impl(long long nelem, int nz, int lognormal, double sigma,
+                              const double* growth, const double* rho, void* d) {
+  if (lognormal && !(sigma > 0)) {
+    double *parts = nullptr, *out = nullptr, h[2];
+    RF_CUDA(cudaMalloc((void**)&parts, sizeof(double) * 2 * 1024));
+    RF_CUDA(cudaMalloc((void**)&out, sizeof(double) * 2));
+    stats_partial_kernel<T><<<1024, 256>>>((const T*)d, nelem, parts);
+    stats_final_kernel<<<1, 256>>>(parts, 1024, out);
+    cudaError_t e = cudaMemcpy(h, out, sizeof(h), cudaMemcpyDeviceToHost);
+    cudaFree(parts); cudaFree(out);
+    RF_CUDA(e);
+    double mean = h[0] / (double)nelem;
+    sigma = std::sqrt(std::max(0.0, h[1] / (double)nelem - mean * mean));
+  }
+  std::vector<T> a(nz), b(nz);
+  for (int z = 0; z < nz; ++z) {
+    if (lognormal) {
+      double t = 1.0 + (sigma * growth[z]) * (sigma * growth[z]);
+      a[z] = (T)(std::sqrt(std::log(t)) / sigma);
+      b[z] = (T)(rho[z] / std::sqrt(t));
+    } else {
+      a[z] = (T)growth[z];
+      b[z] = (T)rho[z];
+    }
+  }
+  T *da = nullptr, *db = nullptr;
+  RF_CUDA(cudaMalloc((void**)&da, sizeof(T) * nz));
+  RF_CUDA(cudaMalloc((void**)&db, sizeof(T) * nz));
+  cudaMemcpy(da, a.data(), sizeof(T) * nz, cudaMemcpyHostToDevice);
+  cudaMemcpy(db, b.data(), sizeof(T) * nz, cudaMemcpyHostToDevice);
+  density_kernel<T><<<grid_for(nelem), 256>>>((T*)d, nelem, nz, da, db, lognormal);
+  cudaError_t e = cudaDeviceSynchronize();
+  cudaFree(da); cudaFree(db);
+  RF_CUDA(e);
+  return RF_OK;
+}
+
+extern "C" int rf_stage_density(long long nelem, int nz, int dtype, int lognormal, double sigma,
+                                const double* growth, const double* rho, void* host) {
+  if (!host || !growth || !rho || nz <= 0 || nelem <= 0 || nelem % nz)
+    return fail(RF_ERR_ARG, "rf_stage_density: bad argument");
+  const size_t es = dtype == RF_F32 ? 4 : 8;
+  return with_device_copy(host, es * nelem, [&](void* d) {
+    return dtype == RF_F32 ? stage_density_impl<float>(nelem, nz, lognormal, sigma, growth, rho, d)
+                           : stage_density_impl<double>(nelem, nz, lognormal, sigma, growth, rho, d);
+  });
+}

@@ -1,0 +1,243 @@
+"""GPU-backed mirror of randomfield.generate.Generator (reference: randomfield/generate.py).
+
+Constructor and method signatures, attributes, return shapes/dtypes and exceptions follow the
+reference; the seed -> delta(x) pipeline, the density conversion and the Newtonian potential
+run as CUDA kernels in librf_b200.so.  Differences a user can observe:
+
+* deviates come from Philox4x32-10 instead of MT19937 (same statistics, same
+  reproducibility-by-seed), unless white noise is injected with :meth:`set_white_noise`;
+* ``save_potential`` does not allocate a second k-space buffer: the potential source field is
+  regenerated from (seed, smoothing) when :meth:`calculate_newtonian_potential` runs;
+  ``generator.potential`` materialises the reference's array on first access;
+* returned arrays are views of one page-locked host buffer that later calls overwrite (the
+  reference returns views of its single work buffer with the same caveat); the device copy
+  is available zero-copy through :meth:`device_field`.
+"""
+from __future__ import print_function, division
+
+import os
+
+import numpy as np
+import scipy.interpolate
+
+from . import _lib
+from . import cosmotools
+from . import powertools
+from . import transform
+
+_H0_PER_S = 100.0 * 1.0e3 / 3.0856775814913673e22   # 100 km/s/Mpc in 1/s
+_C_KM_S = 299792.458
+
+
+class _PlanView(object):
+    """What the reference exposes as ``generator.plan_c2r`` / ``plan_r2c``: shapes, byte
+    counts and lazily materialised host arrays (transform.py:190-244)."""
+
+    def __init__(self, generator, inverse, nbytes):
+        self._g = generator
+        self.shape = (generator._engine.nx, generator._engine.ny, generator._engine.nz)
+        self.inverse, self.packed, self.overwrite, self.use_pyfftw = inverse, True, True, False
+        self.nbytes_allocated = nbytes
+
+    @property
+    def data_out(self):
+        if self.inverse:
+            return self._g._host_field()
+        return self._g._host_kspace()
+
+    @property
+    def data_in(self):
+        if self.inverse:
+            return self._g._host_kspace()
+        return self._g._host_field()
+
+
+class Generator(object):
+    """Manage random field generation for a specified geometry (generate.py:21-142).
+
+    Parameters are those of the reference: ``nx, ny, nz`` grid sizes (all even), uniform
+    ``grid_spacing_Mpc_h``, ``num_plot_sections`` (must divide nz), optional ``cosmology``
+    (anything with the astropy FLRW attributes used here), optional tabulated ``power`` and
+    ``verbose``.  ``dtype`` (extension, default float32 like the reference's complex64 plan)
+    selects float64 arithmetic.
+    """
+
+    def __init__(self, nx, ny, nz, grid_spacing_Mpc_h, num_plot_sections=4,
+                 cosmology=None, power=None, verbose=False, dtype=np.float32):
+        if nx % 2 or ny % 2 or nz % 2:
+            raise ValueError('All shape dimensions must be even.')
+        self._engine = _lib.Engine(nx, ny, nz, dtype=dtype)
+        self._real_dtype = self._engine.real_dtype
+        self._shape = (nx, ny, nz)
+        itemsize = self._engine.complex_dtype.itemsize
+        self.plan_c2r = _PlanView(self, True, nx * ny * (nz // 2 + 1) * itemsize)
+        self.plan_r2c = _PlanView(self, False, 0)
+        self.grid_spacing_Mpc_h = grid_spacing_Mpc_h
+        k0 = (2 * np.pi) / grid_spacing_Mpc_h
+        self.k_min, self.k_max = k0 / max(nx, ny, nz), k0 * np.sqrt(3) / 2
+        self._potential_args = None
+        self._potential_cache = None
+        self._noise = None
+        self._host = None
+        self._field_kind = None
+        self._last = None
+
+        if nz % num_plot_sections != 0:
+            raise ValueError('Z-axis does not evenly divided into {0} plot sections.'
+                             .format(num_plot_sections))
+        self.num_plot_sections = num_plot_sections
+
+        if cosmology is None:
+            self.cosmology = cosmotools.create_cosmology()
+            if power is None:
+                power = powertools.load_default_power()
+        else:
+            self.cosmology = cosmology
+            if power is None:
+                raise RuntimeError('power.calculate_power requires classy.')
+        self.power = powertools.validate_power(power)
+
+        probe = np.empty((1, 1, nz), dtype=self._real_dtype)
+        self.redshifts = cosmotools.get_redshifts(
+            self.cosmology, probe, spacing=self.grid_spacing_Mpc_h, scaled_by_h=True,
+            z_axis=2).reshape(nz)
+        self.redshift_to_index = scipy.interpolate.interp1d(
+            self.redshifts, np.arange(nz), kind='linear', bounds_error=False)
+        self.DC = np.arange(nz) * self.grid_spacing_Mpc_h
+        self.DA = cosmotools._value(
+            self.cosmology.comoving_transverse_distance(self.redshifts),
+            cosmotools._u.Mpc if cosmotools._u is not None else None) * self.cosmology.h
+        self.angular_spacing = self.DA * (np.pi / 180.) / self.grid_spacing_Mpc_h
+        self.z_max = self.redshifts.flat[-1]
+        self.x_fov = nx / self.angular_spacing.flat[-1]
+        self.y_fov = ny / self.angular_spacing.flat[-1]
+        self.growth_function = cosmotools.get_growth_function(self.cosmology, self.redshifts)
+        self.mean_matter_density = cosmotools.get_mean_matter_densities(
+            self.cosmology, self.redshifts)
+
+        self.verbose = verbose
+        if self.verbose:
+            Mb = (self.plan_c2r.nbytes_allocated + self.plan_r2c.nbytes_allocated) / 2.0 ** 20
+            print('Allocated {0:.1f} Mb for {1} x {2} x {3} grid.'.format(Mb, nx, ny, nz))
+            print('{0} Mpc/h spacing covered by k = {1:.5f} - {2:.5f} h/Mpc.'
+                  .format(self.grid_spacing_Mpc_h, self.k_min, self.k_max))
+            print('Grid has z < {0:.3f} with {1:.4f} deg x {2:.4f} deg'
+                  .format(self.z_max, self.x_fov, self.y_fov),
+                  ' = {0:.4f} deg**2 field of view.'.format(self.x_fov * self.y_fov))
+
+    # ------------------------------------------------------------------ host/device views
+    def _host_field(self):
+        """Host copy of the device real field in the generator's page-locked buffer."""
+        if self._host is None:
+            self._host = _lib.PinnedArray(self._shape, self._real_dtype)
+        self._engine.copy_field(self._host.array)
+        return self._host.array
+
+    def _host_kspace(self):
+        if self._last is None:
+            raise RuntimeError('No k-space field has been generated yet.')
+        seed, _ = self._last
+        return self._engine.kspace_public(seed, potential=False)
+
+    def device_field(self):
+        """The current real field as a torch CUDA tensor sharing the library's memory."""
+        return self._engine.field_tensor()
+
+    def set_white_noise(self, noise):
+        """Inject white noise: ``2*nx*ny*(nz//2+1)`` float64 standard-normal deviates in the
+        order ``RandomState.normal(size)`` fills the reference's buffer (random.py:17-28).
+        ``None`` returns to the Philox generator."""
+        self._engine.set_noise(noise)
+        self._noise = noise is not None
+
+    @property
+    def potential(self):
+        """delta(k)/k**2 in the public (nx, ny, nz//2+1) layout (generate.py:200-215), or
+        None when the last field was generated with ``save_potential=False``."""
+        if self._potential_args is None:
+            return None
+        if self._potential_cache is None:
+            self._load_table(self._potential_args[1])
+            self._potential_cache = self._engine.kspace_public(self._potential_args[0], potential=True)
+            self._field_kind = None
+        return self._potential_cache
+
+    def _load_table(self, smoothing):
+        self.smoothed_power = powertools.filter_power(self.power, smoothing)
+        k, sigma = powertools.sigma_table(self.smoothed_power, self._shape, self.grid_spacing_Mpc_h)
+        self._engine.set_power(k, sigma, self.grid_spacing_Mpc_h)
+
+    # ------------------------------------------------------------------ the hot path
+    def generate_delta_field(self, smoothing_length_Mpc_h=0., seed=None,
+                             save_potential=True, show_plot=False, save_plot_name=None):
+        """Generate a delta-field realization (generate.py:144-230).
+
+        Returns a float32 (or float64) array of shape (nx, ny, nz): a view of this
+        generator's host buffer that later calls overwrite."""
+        if seed is None:
+            seed = int.from_bytes(os.urandom(8), 'little')
+        self._load_table(smoothing_length_Mpc_h)
+        self._engine.generate_delta(seed, potential=False, zscale=None, want_stats=True)
+        s1, s2, n = self._engine.stats()
+        mean = s1 / n
+        self.delta_field_rms = self._real_dtype.type(np.sqrt(max(s2 / n - mean * mean, 0.)))
+        self._last = (seed, smoothing_length_Mpc_h)
+        self._potential_args = (seed, smoothing_length_Mpc_h) if save_potential else None
+        self._potential_cache = None
+        self._field_kind = 'delta'
+        if self.verbose:
+            print('Delta field has standard deviation {0:.3f}.'.format(self.delta_field_rms))
+        delta = self._host_field()
+        if show_plot or save_plot_name is not None:
+            self.plot_slice(show_plot=show_plot, save_plot_name=save_plot_name,
+                            clip_symmetric=True, label='Matter inhomogeneity ' +
+                            '$\\delta(r) = \\rho(r)/\\overline{\\rho} - 1$')
+        return delta
+
+    def convert_delta_to_density(self, apply_lognormal_transform=True,
+                                 show_plot=False, save_plot_name=None):
+        """Convert the delta field into a light-cone density field in g/cm**3
+        (generate.py:232-280), in place on the device."""
+        if self._field_kind is None:
+            raise RuntimeError('No delta field in the buffer.')
+        self._engine.density(apply_lognormal_transform, float(self.delta_field_rms),
+                             self.growth_function, self.mean_matter_density)
+        self._field_kind = 'density'
+        rho = self._host_field()
+        if show_plot or save_plot_name is not None:
+            self.plot_slice(show_plot=show_plot, save_plot_name=save_plot_name,
+                            label='Matter density $\\rho(r)$ (g/cm$^3$)', clip_percent=2.)
+        return rho
+
+    def calculate_newtonian_potential(self, light_cone=True,
+                                      show_plot=False, save_plot_name=None):
+        """Newtonian potential Phi(r) in s**-2 (generate.py:282-350): inverse transform of
+        -(3/2) H0^2 Om0 delta(k)/k^2, times G(z)/(1+z) on the light cone."""
+        if self._potential_args is None:
+            raise RuntimeError('No saved potential field.')
+        seed, smoothing = self._potential_args
+        scale = -1.5 * _H0_PER_S ** 2 * self.cosmology.Om0
+        zscale = np.full(self._shape[2], scale, dtype=np.float64)
+        if light_cone:
+            zscale = zscale * self.growth_function / (1 + self.redshifts)
+        self._load_table(smoothing)
+        self._engine.generate_delta(seed, potential=True, zscale=zscale, want_stats=False)
+        self._field_kind = 'potential'
+        field = self._host_field()
+        if show_plot or save_plot_name is not None:
+            self.plot_slice(clip_symmetric=True, show_plot=show_plot, save_plot_name=save_plot_name,
+                            label='Newtonian potential $\\Phi(r)$ [s$^{-2}$]')
+        return field
+
+    def calculate_lensing_potential(self, i_min=None, show_plot=False, save_plot_name=None):
+        """generate.py:353-418 is outside the accelerated path."""
+        raise NotImplementedError(
+            'calculate_lensing_potential is not part of the B200 field-synthesis path yet.')
+
+    def plot_slice(self, *args, **kwargs):
+        """generate.py:420-516 needs matplotlib, which is not installed on the GPU box."""
+        try:
+            import matplotlib  # noqa: F401
+        except ImportError:
+            raise ImportError('plot_slice requires matplotlib.')
+        raise NotImplementedError('plot_slice is outside the B200 field-synthesis path.')
