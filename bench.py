@@ -1,0 +1,326 @@
+#!/usr/bin/env python
+"""bench.py -- seed -> delta(x) throughput (Mcells/s) on N B200s of one box.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--grid nx,ny,nz]
+
+A step is one full pass of the hot path (generate + 3 FFT passes) for a new seed.
+Workloads (weak scaling, 1024^3 cells per GPU):
+  N=1: 1024^3 (the single-GPU configuration BASELINE.json's metric is quoted on)
+  N=2: 2048x2048x512 (BASELINE config 4)   N=4: 2048x2048x1024   N=8: 2048^3
+  --grid 4096,4096,4096 --gpus 8 runs the 4096^3 configuration of the metric.
+`value`  : device-timed, nothing crosses PCIe, field left resident in HBM.
+`e2e`    : the same metric through Generator.generate_delta_field() returning a host numpy
+           array (table upload + device->host copy of the field inside the timed region).
+`roofline`: the dominant kernel against the measured HBM copy bandwidth.
+`cpu_baseline`: the reference algorithm (oracle port, numpy, 1 core) on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mcells/s seed->delta(x)"
+UNIT = "Mcells/s"
+SPACING = 2.0
+WEAK_GRIDS = {1: (1024, 1024, 1024), 2: (2048, 2048, 512), 4: (2048, 2048, 1024), 8: (2048, 2048, 2048)}
+BYTES_PER_CELL = 20.0          # f32: write 4 + (read 4 + write 4) x 2   
+PASS_BYTES_PER_CELL = (4.0, 8.0, 8.0)
+PASS_NAMES = ("k1_generate_xfft", "k2_strided_fft", "k3_c2r_lines")
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, val in zip(names, r[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": float(max(mx)) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_step(n, seed):
+    """One pass of the reference algorithm (generate.py:191-219) on the host: the numpy
+    restatement in oracle/oracle.py, bit-identical to the reference modules.  Returns seconds."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle
+    power = oracle.load_default_power()
+    t0 = time.perf_counter()
+    r = oracle.generate_delta_field((n, n, n), SPACING, power, seed=seed, save_potential=False)
+    dt = time.perf_counter() - t0
+    assert np.isfinite(r["rms"])
+    return dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    n = args.cpu_n or 256
+    for w in range(args.warmup):
+        cpu_reference_step(n, 1000 + w)
+    times = [cpu_reference_step(n, 123 + s) for s in range(args.steps)]
+    total = float(np.sum(times))
+    value = args.steps * n ** 3 / total / 1e6
+    grid = parse_grid(args)
+    sample = "%d^3 grid per step (bounded sample of the %s workload), numpy pocketfft + MT19937" % (
+        n, "x".join(map(str, grid)))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": {"workload": workload_name(grid, args.gpus), "cpu_sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def parse_grid(args):
+    if args.grid:
+        g = tuple(int(v) for v in args.grid.split(","))
+        if len(g) == 1:
+            g = g * 3
+        return g
+    if args.gpus not in WEAK_GRIDS:
+        raise SystemExit("--gpus must be 1, 2, 4 or 8 (or pass --grid)")
+    return WEAK_GRIDS[args.gpus]
+
+
+def workload_name(grid, gpus):
+    return "seed->delta(x) %dx%dx%d f32, spacing %.1f Mpc/h, bundled P(k), %d GPU(s)" % (
+        grid[0], grid[1], grid[2], SPACING, gpus)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from randomfield_b200 import powertools
+    from randomfield_b200.slab import SlabEngine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node %d" % args.gpus)
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    grid = parse_grid(args)
+    nx, ny, nz = grid
+    cells = float(nx) * ny * nz
+    power = powertools.load_default_power()
+    eng = SlabEngine(nx, ny, nz, SPACING, power, dtype=np.float32)
+    eng.engine.set_timing(True)
+    stream = eng.stream
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for w in range(max(args.warmup, 3)):
+        eng.generate(9000 + w)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = eng.engine.launch_count
+    pass_ms = np.zeros(3)
+    barrier()
+    ev0.record(stream)
+    for s in range(args.steps):
+        eng.generate(123 + s)
+    ev1.record(stream)
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    launches = eng.engine.launch_count - launches0
+    # per-kernel durations (CUDA events on the launching stream), a few extra steps
+    nprobe = min(args.steps, 5)
+    for s in range(nprobe):
+        eng.generate(500 + s)
+        pass_ms += np.array(eng.engine.get_timing())
+    pass_ms /= nprobe
+    clocks = sampler.stop() if rank == 0 else None
+    mean, std = eng.global_stats()
+    if world > 1:
+        t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+        pm = torch.tensor(pass_ms, dtype=torch.float64, device="cuda")
+        dist.all_reduce(pm, op=dist.ReduceOp.MAX)
+        pass_ms = pm.cpu().numpy()
+    ms_step = ms_total / args.steps
+    value = cells / (ms_step * 1e-3) / 1e6
+
+    # ---- end to end through the public API (N=1: Generator; N>1: slab + host copy) ------
+    e2e = None
+    if rank == 0 or world > 1:
+        e2e = run_e2e(args, grid, world, rank, eng, barrier)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peak, peak_src = measured_peaks()
+    local_cells = cells / world
+    dom = int(np.argmax(pass_ms))
+    dom_bytes = PASS_BYTES_PER_CELL[dom] * local_cells
+    achieved = dom_bytes / (pass_ms[dom] * 1e-3) / 1e9
+    step_achieved = BYTES_PER_CELL * local_cells / (ms_step * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(grid, world), "grid": list(grid),
+                   "l2": "working set %.1f GB per GPU >> 126 MB L2, no flush needed" % (4 * local_cells / 1e9),
+                   "parallelism": "y-slab k-space -> all-to-all -> x-slab real space" if world > 1 else "single GPU",
+                   "field_std": std, "field_mean": mean},
+        "roofline": {"bound": "hbm", "kernel": PASS_NAMES[dom], "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": dom_bytes},
+        "roofline_step": {"bytes_per_cell": BYTES_PER_CELL, "achieved": step_achieved, "peak": peak,
+                          "unit": "GB/s", "frac": step_achieved / peak,
+                          "frac_of_8TBs": step_achieved / 8000.0},
+        "kernels_ms": dict(zip(PASS_NAMES, [float(v) for v in pass_ms])),
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+    }
+    if world > 1:
+        nvl_bytes = eng.exchange_bytes
+        line["config"]["all_to_all_bytes_per_gpu"] = nvl_bytes
+    if args.cpu_n != 0 and world == 1:
+        n = args.cpu_n or 512
+        sec = cpu_reference_step(n, 123)
+        line["cpu_baseline"] = {
+            "value": n ** 3 / sec / 1e6, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": "%d^3 grid, one pass of the reference algorithm (oracle port: numpy pocketfft "
+                      "irfftn + MT19937 normal), %.1f s" % (n, sec)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def run_e2e(args, grid, world, rank, eng, barrier):
+    """Same metric through the call a user makes, host array out."""
+    import torch
+    import torch.distributed as dist
+    nx, ny, nz = grid
+    cells = float(nx) * ny * nz
+    steps = max(1, min(args.steps, 3))
+    if world == 1:
+        import randomfield_b200 as rf
+        eng.engine.close()
+        gen = rf.Generator(nx, ny, nz, SPACING)
+        gen.generate_delta_field(seed=1, save_potential=False)      # warm-up: pins the host buffer
+        t0 = time.perf_counter()
+        for s in range(steps):
+            out = gen.generate_delta_field(seed=123 + s, save_potential=False)
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / steps
+        h2d = 2 * 8 * len(gen.power) + 8
+        d2h = out.nbytes + 16
+        assert out.shape == (nx, ny, nz) and np.isfinite(out[0, 0, 0])
+    else:
+        from randomfield_b200 import _lib
+        host = _lib.PinnedArray(eng.engine.field_shape, np.float32)
+        eng.generate(1)
+        eng.engine.copy_field(host.array)
+        barrier()
+        t0 = time.perf_counter()
+        for s in range(steps):
+            eng.generate(123 + s)
+            eng.engine.copy_field(host.array)
+        barrier()
+        dt = (time.perf_counter() - t0) / steps
+        t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+        h2d, d2h = 8, host.array.nbytes + 16
+    return {"value": cells / dt / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "ms_per_step": dt * 1e3, "steps": steps,
+            "api": "randomfield_b200.Generator.generate_delta_field -> numpy" if world == 1
+                   else "SlabEngine.generate + copy_field -> pinned numpy (per rank x-slab)"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--grid", default=None, help="nx,ny,nz override")
+    ap.add_argument("--cpu-n", type=int, default=None,
+                    help="cube size of the CPU baseline sample (0 disables it in the GPU arm)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -122,6 +122,12 @@ int rf_stage_density(long long nelem, int nz, int dtype, int lognormal, double s
 void* rf_host_alloc(long long bytes);
 void rf_host_free(void* p);
 
+/* per-kernel device timing: when enabled, CUDA events bracket the three hot-path kernels on
+ * the context's stream; rf_get_timing synchronises and returns the last step's durations in
+ * milliseconds (pass 1 generate+x, pass 2 y, pass 3 z/c2r). */
+int rf_set_timing(rf_ctx* ctx, int enabled);
+int rf_get_timing(rf_ctx* ctx, double* ms_pass1, double* ms_pass2, double* ms_pass3);
+
 /* raw device pointers for zero-copy wrapping (torch / DLPack) and for the all-to-all */
 void* rf_device_ptr(rf_ctx* ctx, int which);
 long long rf_buffer_bytes(rf_ctx* ctx, int which);

@@ -45,6 +45,8 @@ SIGNATURES = {
     "rf_stage_density": (_c.c_int, [_c.c_longlong, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _P, _P, _P]),
     "rf_host_alloc": (_P, [_c.c_longlong]),
     "rf_host_free": (None, [_P]),
+    "rf_set_timing": (_c.c_int, [_P, _c.c_int]),
+    "rf_get_timing": (_c.c_int, [_P, _c.POINTER(_c.c_double), _c.POINTER(_c.c_double), _c.POINTER(_c.c_double)]),
     "rf_device_ptr": (_P, [_P, _c.c_int]),
     "rf_buffer_bytes": (_c.c_longlong, [_P, _c.c_int]),
     "rf_is_fast": (_c.c_int, [_P]),
@@ -186,6 +188,15 @@ class Engine:
         g = np.ascontiguousarray(np.broadcast_to(np.asarray(growth, dtype=np.float64).reshape(-1), (self.nz,)))
         r = np.ascontiguousarray(np.broadcast_to(np.asarray(rho, dtype=np.float64).reshape(-1), (self.nz,)))
         check(lib().rf_density(self._ctx, int(bool(lognormal)), float(sigma), ptr(g), ptr(r)))
+
+    def set_timing(self, enabled=True):
+        check(lib().rf_set_timing(self._ctx, int(bool(enabled))))
+
+    def get_timing(self):
+        """(pass1, pass2, pass3) milliseconds of the last step (synchronises)."""
+        t = [ctypes.c_double() for _ in range(3)]
+        check(lib().rf_get_timing(self._ctx, *[ctypes.byref(x) for x in t]), value_error_ok=False)
+        return tuple(x.value for x in t)
 
     def sync(self):
         check(lib().rf_sync(self._ctx))

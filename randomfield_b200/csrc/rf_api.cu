@@ -59,7 +59,13 @@ struct rf_ctx {
   void *zs_dev = nullptr, *da_dev = nullptr, *db_dev = nullptr;   // nz-length tables of T
   long long launches = 0;
   bool field_is_real = false;
+  bool timing = false;
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
+
+static void mark(rf_ctx* c, int i) {
+  if (c->timing) cudaEventRecord(c->ev[i], c->stream);
+}
 
 static bool is_pow2(int n) { return n > 0 && (n & (n - 1)) == 0; }
 static bool fast_size(int n) { return is_pow2(n) && n >= 64 && n <= 4096; }
@@ -162,6 +168,23 @@ extern "C" void* rf_host_alloc(long long bytes) {
 }
 extern "C" void rf_host_free(void* p) {
   if (p) cudaFreeHost(p);
+}
+extern "C" int rf_set_timing(rf_ctx* c, int enabled) {
+  if (!c) return fail(RF_ERR_ARG, "null ctx");
+  if (enabled && !c->ev[0])
+    for (int i = 0; i < 6; ++i) RF_CUDA(cudaEventCreate(&c->ev[i]));
+  c->timing = enabled != 0;
+  return RF_OK;
+}
+extern "C" int rf_get_timing(rf_ctx* c, double* a, double* b, double* d) {
+  if (!c || !c->timing || !c->fast) return fail(RF_ERR_STATE, "rf_get_timing: timing is off or generic path");
+  RF_CUDA(cudaStreamSynchronize(c->stream));
+  float t[3] = {0, 0, 0};
+  for (int i = 0; i < 3; ++i) RF_CUDA(cudaEventElapsedTime(&t[i], c->ev[2 * i], c->ev[2 * i + 1]));
+  if (a) *a = t[0];
+  if (b) *b = t[1];
+  if (d) *d = t[2];
+  return RF_OK;
 }
 extern "C" int rf_is_fast(rf_ctx* c) { return c && c->fast ? 1 : 0; }
 extern "C" long long rf_launch_count(rf_ctx* c) { return c ? c->launches : 0; }
@@ -369,7 +392,9 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
     int e = 0;
     RF_DISPATCH_N(c->nx, {
       int grid = c->nyl * ((c->nz / 2) / FftPlan<T, NN>::TZ);
+      mark(c, 0);
       e = Launch<T, NN>::k1(c->noise != nullptr, p, grid, c->stream);
+      mark(c, 1);
     });
     c->launches++;
     RF_CUDA(e);
@@ -439,7 +464,9 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
     int e = 0;
     RF_DISPATCH_N(c->ny, {
       int grid = c->nxl * (nzc / FftPlan<T, NN>::TZ);
+      mark(c, 2);
       e = Launch<T, NN>::k2(true, p2, grid, c->stream);
+      mark(c, 3);
     });
     c->launches++;
     RF_CUDA(e);
@@ -458,7 +485,9 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
         if (e2) return e2;
         p3.partials = c->partials;
       }
+      mark(c, 4);
       e = Launch<T, NN>::k3(p3, (int)grid, c->stream);
+      mark(c, 5);
     });
     c->launches++;
     RF_CUDA(e);

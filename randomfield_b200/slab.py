@@ -1,0 +1,99 @@
+"""Slab decomposition of the seed -> delta(x) path across the GPUs of one box.
+
+One process per GPU (torch.distributed, backend "nccl").  Rank g generates the k-space
+y-slab ``iy in [g*ny/G, (g+1)*ny/G)`` for every x (pass 1 is local because every x line is
+complete), the ranks exchange one all-to-all of the half-complex field, and rank g finishes
+the x-slab ``ix in [g*nx/G, (g+1)*nx/G)`` (passes 2 and 3 are local).  Concatenating the ranks'
+results along axis 0 gives the reference's C-order (nx, ny, nz) array.  Mode generation is
+counter-based, so the field is bit-identical for every G.
+
+Buffer layouts (complex elements, nzc = nz/2):
+  send  [nx][ny/G][nzc]            == [G dest][nx/G][ny/G][nzc]  (dest blocks are contiguous)
+  recv  [G src][nx/G][ny/G][nzc]   row y of pass 2 lives in block y // (ny/G)
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import _lib
+from . import powertools
+
+
+def slab_ranges(n, world, rank):
+    """[lo, hi) owned by `rank` when an axis of length n is split over `world` ranks."""
+    if n % world:
+        raise ValueError("axis length {0} is not divisible by {1} ranks".format(n, world))
+    step = n // world
+    return rank * step, (rank + 1) * step
+
+
+def block_elems(nx, ny, nz, world):
+    """Complex elements in one all-to-all block: (nx/G) * (ny/G) * (nz/2)."""
+    return (nx // world) * (ny // world) * (nz // 2)
+
+
+def recv_to_rows(recv, nx, ny, nz, world):
+    """Reorder a receive buffer [G src][nx/G][ny/G][nzc] into [nx/G][ny][nzc] (what pass 2
+    reads through its row map).  Host-side restatement used by the CPU tests."""
+    nxl, nyl, nzc = nx // world, ny // world, nz // 2
+    r = np.asarray(recv).reshape(world, nxl, nyl, nzc)
+    return np.ascontiguousarray(np.transpose(r, (1, 0, 2, 3)).reshape(nxl, ny, nzc))
+
+
+def all_to_all(send, recv, group=None):
+    """One all-to-all of `world` equal contiguous blocks (torch tensors, any backend)."""
+    import torch.distributed as dist
+    dist.all_to_all_single(recv, send, group=group)
+
+
+class SlabEngine(object):
+    """The device side of a slab-decomposed Generator on this rank."""
+
+    def __init__(self, nx, ny, nz, spacing, power, smoothing=0.0, dtype=np.float32, group=None):
+        import torch
+        import torch.distributed as dist
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.shape = (nx, ny, nz)
+        self.engine = _lib.Engine(nx, ny, nz, dtype=dtype, rank=self.rank, world=self.world)
+        k, sig = powertools.sigma_table(powertools.filter_power(power, smoothing), self.shape, spacing)
+        self.engine.set_power(k, sig, spacing)
+        self.stream = torch.cuda.Stream()
+        self.engine.set_stream(self.stream.cuda_stream)
+        itemsize = self.engine.complex_dtype.itemsize
+        self._xfer_bytes = nx * (ny // self.world) * (nz // 2) * itemsize
+        if self.world > 1:
+            self._send = self.engine.torch_view(_lib.RF_BUF_FIELD, self._xfer_bytes)
+            self._recv = self.engine.torch_view(_lib.RF_BUF_RECV, self._xfer_bytes)
+
+    @property
+    def exchange_bytes(self):
+        """Bytes this rank sends to other ranks per step."""
+        return self._xfer_bytes * (self.world - 1) // self.world
+
+    def generate(self, seed, potential=False, zscale=None, want_stats=True):
+        """seed -> this rank's real-space x-slab, left resident on the device."""
+        import torch
+        with torch.cuda.stream(self.stream):
+            if self.world == 1:
+                self.engine.generate_delta(seed, potential, zscale, want_stats)
+            else:
+                self.engine.generate_xpass(seed, potential)
+                all_to_all(self._send, self._recv, self.group)
+                self.engine.finish_yz(zscale, want_stats)
+
+    def global_stats(self):
+        """(mean, std) of the whole field: local sums combined across ranks."""
+        import torch
+        import torch.distributed as dist
+        s1, s2, n = self.engine.stats()
+        if self.world > 1:
+            t = torch.tensor([s1, s2, float(n)], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, group=self.group)
+            s1, s2, n = (float(v) for v in t.tolist())
+        mean = s1 / n
+        return mean, float(np.sqrt(max(s2 / n - mean * mean, 0.0)))
+
+    def local_field(self):
+        return self.engine.copy_field()
