@@ -217,7 +217,7 @@ def run_ours(args):
 
     # ---- end to end through the public API (N=1: Generator; N>1: slab + host copy) ------
     e2e = None
-    if rank == 0 or world > 1:
+    if (rank == 0 or world > 1) and not args.no_e2e:
         e2e = run_e2e(args, grid, world, rank, eng, barrier)
 
     if rank != 0:
@@ -316,6 +316,7 @@ def main():
     ap.add_argument("--grid", default=None, help="nx,ny,nz override")
     ap.add_argument("--cpu-n", type=int, default=None,
                     help="cube size of the CPU baseline sample (0 disables it in the GPU arm)")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
