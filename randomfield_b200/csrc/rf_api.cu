@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <limits>
 #include <string>
 #include <vector>
 
@@ -51,8 +52,8 @@ struct rf_ctx {
   void *tw_x = nullptr, *tw_y = nullptr, *tw_z = nullptr, *tw_zh = nullptr;
   // sigma table
   void* knots = nullptr;
-  int16_t* lut = nullptr;
-  int ntab = 0, lut_n = 0, lut_base = 0;
+  void* cells = nullptr;
+  int ntab = 0, lut_n = 0, lut_base = 0, lut_shift = 0;
   double spacing = 0.0;
   bool have_power = false;
   double* noise = nullptr;
@@ -139,7 +140,7 @@ extern "C" int rf_destroy(rf_ctx* c) {
   if (!c) return RF_OK;
   cudaStreamSynchronize(c->stream);
   void* ptrs[] = {c->field, c->recv, c->partials, c->stats_dev, c->tw_x, c->tw_y, c->tw_z,
-                  c->tw_zh, c->knots, c->lut, c->noise, c->zs_dev, c->da_dev, c->db_dev};
+                  c->tw_zh, c->knots, c->cells, c->noise, c->zs_dev, c->da_dev, c->db_dev};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -213,66 +214,100 @@ extern "C" long long rf_buffer_bytes(rf_ctx* c, int which) {
 // ------------------------------------------------------------------------------------------
 // sigma table
 // ------------------------------------------------------------------------------------------
-static int cell_of(float v) {
+template <typename T> struct FloatBits;
+template <> struct FloatBits<float> { static constexpr int kMant = 23; };   // bits below the exponent
+template <> struct FloatBits<double> { static constexpr int kMant = 20; };  // ... in the high word
+
+static int cell_of(float v, int shift) {
   int32_t b;
   memcpy(&b, &v, 4);
-  return b >> 19;
+  return b >> shift;
 }
-static int cell_of(double v) {
+static int cell_of(double v, int shift) {
   int64_t b;
   memcpy(&b, &v, 8);
-  return (int)(b >> 48);
-}
-static float cell_floor(int cell, float) {
-  int32_t b = cell << 19;
-  float v;
-  memcpy(&v, &b, 4);
-  return v;
-}
-static double cell_floor(int cell, double) {
-  int64_t b = (int64_t)cell << 48;
-  double v;
-  memcpy(&v, &b, 8);
-  return v;
+  return (int)((int32_t)(b >> 32) >> shift);
 }
 
+// Builds the knot array and the direct-indexed cell table described in rf_common.cuh.
 template <typename T>
 static int build_table(rf_ctx* c, int n, const double* k, const double* sigma) {
   const double N3 = (double)c->nx * c->ny * c->nz;
   std::vector<knot<T>> kn(n);
-  std::vector<double> l2(n), sg(n);
+  std::vector<double> l2(n), sg(n), slope(n, 0.0);
   for (int j = 0; j < n; ++j) {
     kn[j].ksq = (T)(k[j] * k[j]);
     l2[j] = 2.0 * std::log2(k[j]);
     sg[j] = sigma[j] / N3;
   }
   for (int j = 0; j < n; ++j) {
+    if (j + 1 < n) slope[j] = (sg[j + 1] - sg[j]) / (l2[j + 1] - l2[j]);
     kn[j].l2 = (T)l2[j];
     kn[j].sig = (T)sg[j];
-    kn[j].slope = (j + 1 < n) ? (T)((sg[j + 1] - sg[j]) / (l2[j + 1] - l2[j])) : (T)0;
+    kn[j].slope = (T)slope[j];
     if (j > 0 && !(kn[j].ksq > kn[j - 1].ksq))
       return fail(RF_ERR_ARG, "Power spectrum k values are not strictly increasing.");
   }
-  const int base = cell_of(kn[0].ksq) - 1;
-  const int ln = cell_of(kn[n - 1].ksq) - base + 1;
-  if (ln <= 0 || ln > (1 << 20)) return fail(RF_ERR_ARG, "rf_set_power: bad k range");
-  std::vector<int16_t> lut(ln);
-  int cnt = 0;
-  for (int e = 0; e < ln; ++e) {
-    T edge = cell_floor(base + e, (T)0);
-    while (cnt < n && kn[cnt].ksq <= edge) ++cnt;
-    lut[e] = (int16_t)(cnt - 1);
+  // mantissa bits per cell: the fewest (4..8) that leave at most one knot per cell
+  int mb = 4, shift = 0, base = 0, ln = 0;
+  for (;; ++mb) {
+    shift = FloatBits<T>::kMant - mb;
+    base = cell_of(kn[0].ksq, shift) - 1;
+    ln = cell_of(kn[n - 1].ksq, shift) - base + 2;
+    int worst = 1;
+    for (int j = 1, run = 1; j < n; ++j) {
+      run = (cell_of(kn[j].ksq, shift) == cell_of(kn[j - 1].ksq, shift)) ? run + 1 : 1;
+      worst = std::max(worst, run);
+    }
+    if (worst <= 1 || mb == 8) break;
+  }
+  if (ln < 3 || ln > (1 << 22)) return fail(RF_ERR_ARG, "rf_set_power: bad k range");
+  const T inf = std::numeric_limits<T>::infinity();
+  auto zero_cell = [&](int bin) {
+    sigcell<T> z;
+    z.c0a = z.c1a = z.c0b = z.c1b = (T)0; z.t = inf; z.bin_a = (T)bin; z.slow = (T)0; z.pad = (T)0;
+    return z;
+  };
+  // sigma = c0 + c1*lg on segment j, anchored at the segment midpoint so that the rounding of
+  // c1 to T costs nothing there
+  auto seg_coef = [&](int j, T& c0, T& c1) {
+    c1 = (T)slope[j];
+    const double mid = 0.5 * (l2[j] + l2[j + 1]);
+    c0 = (T)((sg[j] + slope[j] * (mid - l2[j])) - (double)c1 * mid);
+  };
+  std::vector<sigcell<T>> cells(ln);
+  cells[0] = zero_cell(-1);
+  cells[ln - 1] = zero_cell(n - 1);
+  int next = 0;   // first knot not below the current cell
+  for (int e = 1; e < ln - 1; ++e) {
+    const int id = base + e;
+    while (next < n && cell_of(kn[next].ksq, shift) < id) ++next;
+    int cnt = 0;
+    while (next + cnt < n && cell_of(kn[next + cnt].ksq, shift) == id) ++cnt;
+    const int jlo = next - 1;
+    sigcell<T> s = zero_cell(jlo);
+    if (cnt == 0) {
+      seg_coef(jlo, s.c0a, s.c1a);
+      s.c0b = s.c0a; s.c1b = s.c1a;
+    } else if (cnt == 1 && next < n - 1) {
+      if (jlo >= 0) seg_coef(jlo, s.c0a, s.c1a);
+      seg_coef(next, s.c0b, s.c1b);
+      s.t = kn[next].ksq;
+    } else {
+      s.slow = (T)1;
+    }
+    cells[e] = s;
   }
   if (c->knots) cudaFree(c->knots);
-  if (c->lut) cudaFree(c->lut);
-  c->knots = nullptr; c->lut = nullptr;
+  if (c->cells) cudaFree(c->cells);
+  c->knots = nullptr; c->cells = nullptr;
   RF_CUDA(cudaMalloc(&c->knots, sizeof(knot<T>) * n));
-  RF_CUDA(cudaMalloc((void**)&c->lut, sizeof(int16_t) * ln));
+  RF_CUDA(cudaMalloc(&c->cells, sizeof(sigcell<T>) * ln));
   // the table may be replaced while earlier work is still queued on the stream
   RF_CUDA(cudaStreamSynchronize(c->stream));
   RF_CUDA(cudaMemcpy(c->knots, kn.data(), sizeof(knot<T>) * n, cudaMemcpyHostToDevice));
-  RF_CUDA(cudaMemcpy(c->lut, lut.data(), sizeof(int16_t) * ln, cudaMemcpyHostToDevice));
-  c->ntab = n; c->lut_n = ln; c->lut_base = base;
+  RF_CUDA(cudaMemcpy(c->cells, cells.data(), sizeof(sigcell<T>) * ln, cudaMemcpyHostToDevice));
+  c->ntab = n; c->lut_n = ln; c->lut_base = base; c->lut_shift = shift;
   return RF_OK;
 }
 
@@ -324,8 +359,8 @@ static ModeGeom<T> make_geom(rf_ctx* c, uint64_t seed, int potential) {
 template <typename T>
 static SigmaTable<T> make_tab(rf_ctx* c) {
   SigmaTable<T> t;
-  t.knots = (const knot<T>*)c->knots; t.lut = c->lut;
-  t.n = c->ntab; t.lut_n = c->lut_n; t.lut_base = c->lut_base;
+  t.knots = (const knot<T>*)c->knots; t.cells = (const sigcell<T>*)c->cells;
+  t.n = c->ntab; t.lut_n = c->lut_n; t.lut_base = c->lut_base; t.shift = c->lut_shift;
   return t;
 }
 

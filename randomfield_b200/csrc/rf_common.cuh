@@ -190,6 +190,16 @@ __device__ __forceinline__ cpx<double> box_muller<double>(uint32_t wa, uint32_t 
 
 // ----------------------------------------------------------------------------------------
 // sigma(k) table in device memory (built on the host by rf_set_power)
+//
+// knots[j]   : the user's table (k_j^2, log2 k_j^2, sigma_j, slope on segment j).
+// cells[c]   : direct-indexed lookup.  Cell c covers the k^2 values whose float bit pattern,
+//              shifted right by `shift`, equals lut_base + c (exponent + a few mantissa bits,
+//              so cells are uniform inside each octave).  The host picks enough mantissa
+//              bits that a cell holds at most one knot, which makes the evaluation
+//              branch-free: sigma = c0 + c1*log2(k^2) with (c0, c1) of the segment below
+//              (A) or above (B) the knot `t` inside the cell.  Cells that would hold more
+//              than one knot, and the cell of the last knot, are flagged and take the
+//              knot-walking path.
 // ----------------------------------------------------------------------------------------
 template <typename T>
 struct alignas(4 * sizeof(T)) knot {
@@ -200,41 +210,77 @@ struct alignas(4 * sizeof(T)) knot {
 };
 
 template <typename T>
-struct SigmaTable {
-  const knot<T>* knots;   // n entries
-  const int16_t* lut;     // lut_n entries: start bin for each coarse cell
-  int n;
-  int lut_n;
-  int lut_base;           // coarse-cell id of lut[0]
+struct alignas(8 * sizeof(T)) sigcell {
+  T c0a, c1a, c0b, c1b;   // sigma = c0 + c1 * log2(k^2) below / at-or-above t
+  T t;                    // knot inside the cell (k^2), +inf if none
+  T bin_a;                // canonical bin index below t, stored as a number (exact)
+  T slow;                 // != 0: walk the knots instead
+  T pad;
 };
 
-// coarse cell id: exponent + 4 mantissa bits of k^2 (16 cells per octave)
-__device__ __forceinline__ int coarse_cell(float v) { return __float_as_int(v) >> 19; }
-__device__ __forceinline__ int coarse_cell(double v) { return __double2hiint(v) >> 16; }
+template <typename T>
+struct SigmaTable {
+  const knot<T>* knots;     // n entries
+  const sigcell<T>* cells;  // lut_n entries; first and last are all-zero sentinels
+  int n;
+  int lut_n;
+  int lut_base;             // cell id of cells[0]
+  int shift;                // cell id = (high bits of k^2) >> shift
+};
+
+__device__ __forceinline__ int coarse_cell(float v, int shift) { return __float_as_int(v) >> shift; }
+__device__ __forceinline__ int coarse_cell(double v, int shift) { return __double2hiint(v) >> shift; }
 __device__ __forceinline__ float rf_log2(float v) { return __log2f(v); }
 __device__ __forceinline__ double rf_log2(double v) { return log2(v); }
+__device__ __forceinline__ float rf_tiny(float) { return 1.17549435e-38f; }
+__device__ __forceinline__ double rf_tiny(double) { return 2.2250738585072014e-308; }
 
-// canonical bin index: largest j with knots[j].ksq <= ksq, or -1.
+// knot-walking evaluation from a start bin (cells flagged slow).  Returns sigma; *bin
+// receives the canonical bin (largest j with knots[j].ksq <= ksq, or -1).
 template <typename T>
-__device__ __forceinline__ int sigma_bin(const SigmaTable<T>& tab, T ksq) {
-  int e = coarse_cell(ksq) - tab.lut_base;
-  e = max(0, min(e, tab.lut_n - 1));
-  int j = __ldg(tab.lut + e);
+__device__ __noinline__ T sigma_walk(const SigmaTable<T>& tab, T ksq, int j, int* bin) {
   while (j + 1 < tab.n && __ldg(&tab.knots[j + 1].ksq) <= ksq) ++j;
-  return j;
-}
-
-template <typename T>
-__device__ __forceinline__ T sigma_eval(const SigmaTable<T>& tab, T ksq, int* bin_out = nullptr) {
-  int j = sigma_bin(tab, ksq);
-  if (bin_out) *bin_out = j;
-  int seg = min(j, tab.n - 2);
+  *bin = j;
   bool outside = (j < 0) || (j == tab.n - 1 && ksq > __ldg(&tab.knots[tab.n - 1].ksq));
-  seg = max(seg, 0);
+  int seg = max(min(j, tab.n - 2), 0);
   const knot<T>* kp = tab.knots + seg;
   T l2 = __ldg(&kp->l2), sg = __ldg(&kp->sig), sl = __ldg(&kp->slope);
   T v = sg + sl * (rf_log2(ksq) - l2);
   return outside ? (T)0 : v;
+}
+
+template <typename T>
+__device__ __forceinline__ T sigma_eval(const SigmaTable<T>& tab, T ksq, int* bin_out = nullptr) {
+  // cells[0] / cells[lut_n-1] are the all-zero "below the table" / "above the table" cells
+  const int c = min(max(coarse_cell(ksq, tab.shift) - tab.lut_base, 0), tab.lut_n - 1);
+  const sigcell<T>* cp = tab.cells + c;
+  T c0a, c1a, c0b, c1b, t, bin_a, slow;
+  if constexpr (sizeof(T) == 4) {
+    float4 lo = __ldg(reinterpret_cast<const float4*>(cp));
+    float4 hi = __ldg(reinterpret_cast<const float4*>(cp) + 1);
+    c0a = lo.x; c1a = lo.y; c0b = lo.z; c1b = lo.w; t = hi.x; bin_a = hi.y; slow = hi.z;
+  } else {
+    const double2* q = reinterpret_cast<const double2*>(cp);
+    double2 a = __ldg(q), b = __ldg(q + 1), d = __ldg(q + 2), e = __ldg(q + 3);
+    c0a = a.x; c1a = a.y; c0b = b.x; c1b = b.y; t = d.x; bin_a = d.y; slow = e.x;
+  }
+  if (slow != (T)0) {
+    int bin;
+    T v = sigma_walk(tab, ksq, (int)bin_a, &bin);
+    if (bin_out) *bin_out = bin;
+    return v;
+  }
+  const bool up = ksq >= t;
+  if (bin_out) *bin_out = (int)bin_a + (up ? 1 : 0);
+  const T c0 = up ? c0b : c0a, c1 = up ? c1b : c1a;
+  return c0 + c1 * rf_log2(fmax(ksq, rf_tiny((T)0)));
+}
+
+template <typename T>
+__device__ __forceinline__ int sigma_bin(const SigmaTable<T>& tab, T ksq) {
+  int b;
+  (void)sigma_eval(tab, ksq, &b);
+  return b;
 }
 
 // ----------------------------------------------------------------------------------------
