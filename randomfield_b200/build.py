@@ -18,6 +18,7 @@ BUILD = os.path.join(CSRC, "build")
 LIB = os.path.join(HERE, "librf_b200.so")
 
 SIZES = (64, 128, 256, 512, 1024, 2048, 4096)
+PIPE_SIZES = (64, 128, 256, 512, 1024, 2048)
 DTYPES = (("f32", "float"), ("f64", "double"))
 
 NVCC_FLAGS = [
@@ -78,6 +79,12 @@ def build(force: bool = False, verbose: bool = False, jobs: int | None = None) -
             objs.append(obj)
             if want(inst_src, obj):
                 todo.append((inst_src, obj, ["-DRF_INST_T=%s" % ctype, "-DRF_INST_N=%d" % n], verbose))
+    pipe_src = os.path.join(CSRC, "rf_pipe_inst.cu")
+    for n in PIPE_SIZES:
+        obj = os.path.join(BUILD, "pipe_%d.o" % n)
+        objs.append(obj)
+        if want(pipe_src, obj):
+            todo.append((pipe_src, obj, ["-DRF_PIPE_N=%d" % n], verbose))
     if todo:
         nj = jobs or min(len(todo), os.cpu_count() or 4)
         with concurrent.futures.ThreadPoolExecutor(nj) as ex:

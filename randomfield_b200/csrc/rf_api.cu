@@ -39,6 +39,8 @@ struct rf_ctx {
   int nx = 0, ny = 0, nz = 0, dtype = 0, rank = 0, world = 1;
   int nxl = 0, nyl = 0;     // local slab extents
   bool fast = false;
+  bool pipe = false;        // TMA-pipelined kernels (f32, env RF_PIPE != 0)
+  int num_sms = 148;
   size_t esize = 4;         // sizeof(T)
   cudaStream_t own_stream = nullptr, stream = nullptr;
   void* field = nullptr;    // RF_BUF_FIELD
@@ -107,6 +109,13 @@ extern "C" int rf_create(int nx, int ny, int nz, int dtype, int rank, int world,
   if (world > 1 && !c->fast) {
     delete c;
     return fail(RF_ERR_ARG, "rf_create: slab decomposition needs power-of-two dims in [64, 4096]");
+  }
+  {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, dev);
+    const char* env = getenv("RF_PIPE");
+    c->pipe = c->fast && dtype == RF_F32 && !(env && env[0] == '0');
   }
   RF_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
   c->stream = c->own_stream;
@@ -378,6 +387,17 @@ static int ensure_partials(rf_ctx* c, long long n) {
 // ------------------------------------------------------------------------------------------
 // dispatch over the compiled tile-kernel sizes
 // ------------------------------------------------------------------------------------------
+#define RF_DISPATCH_PIPE(N_, ...)                       \
+  switch (N_) {                                         \
+    case 64: { constexpr int NN = 64; __VA_ARGS__; } break;    \
+    case 128: { constexpr int NN = 128; __VA_ARGS__; } break;  \
+    case 256: { constexpr int NN = 256; __VA_ARGS__; } break;  \
+    case 512: { constexpr int NN = 512; __VA_ARGS__; } break;  \
+    case 1024: { constexpr int NN = 1024; __VA_ARGS__; } break;\
+    case 2048: { constexpr int NN = 2048; __VA_ARGS__; } break;\
+    default: return fail(RF_ERR_ARG, "size not compiled");\
+  }
+
 #define RF_DISPATCH_N(N_, ...)                          \
   switch (N_) {                                         \
     case 64: { constexpr int NN = 64; __VA_ARGS__; } break;    \
@@ -505,27 +525,56 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
     });
     c->launches++;
     RF_CUDA(e);
-    K3Params<T> p3;
-    p3.buf = (T*)c->field;
-    p3.nlines = (long long)c->nxl * c->ny;
-    p3.twH = (const cpx<T>*)c->tw_zh;
-    p3.twN = (const cpx<T>*)c->tw_z;
-    p3.zscale = zs;
-    p3.partials = nullptr;
-    RF_DISPATCH_N(c->nz, {
-      int tl = Launch<T, NN>::k3_lines_per_cta();
-      long long grid = (p3.nlines + tl - 1) / tl;
-      if (want_stats) {
-        int e2 = ensure_partials(c, grid);
-        if (e2) return e2;
-        p3.partials = c->partials;
+    bool done3 = false;
+    if constexpr (std::is_same<T, float>::value) {
+      if (c->pipe && c->nz <= 2048) {
+        pipe::K3PParams q;
+        q.buf = (float*)c->field;
+        q.twH = (const cpx<float>*)c->tw_zh;
+        q.twN = (const cpx<float>*)c->tw_z;
+        q.zscale = zs;
+        q.partials = nullptr;
+        RF_DISPATCH_PIPE(c->nz, {
+          const long long nlines = (long long)c->nxl * c->ny;
+          q.ntiles = (int)(nlines / PipeLaunch<NN>::k3p_lines_per_tile());
+          int grid = std::min(q.ntiles, c->num_sms);
+          if (want_stats) {
+            int e2 = ensure_partials(c, grid);
+            if (e2) return e2;
+            q.partials = c->partials;
+          }
+          mark(c, 4);
+          e = PipeLaunch<NN>::k3p(q, grid, c->stream);
+          mark(c, 5);
+        });
+        c->launches++;
+        RF_CUDA(e);
+        done3 = true;
       }
-      mark(c, 4);
-      e = Launch<T, NN>::k3(p3, (int)grid, c->stream);
-      mark(c, 5);
-    });
-    c->launches++;
-    RF_CUDA(e);
+    }
+    if (!done3) {
+    K3Params<T> p3;
+      p3.buf = (T*)c->field;
+      p3.nlines = (long long)c->nxl * c->ny;
+      p3.twH = (const cpx<T>*)c->tw_zh;
+      p3.twN = (const cpx<T>*)c->tw_z;
+      p3.zscale = zs;
+      p3.partials = nullptr;
+      RF_DISPATCH_N(c->nz, {
+        int tl = Launch<T, NN>::k3_lines_per_cta();
+        long long grid = (p3.nlines + tl - 1) / tl;
+        if (want_stats) {
+          int e2 = ensure_partials(c, grid);
+          if (e2) return e2;
+          p3.partials = c->partials;
+        }
+        mark(c, 4);
+        e = Launch<T, NN>::k3(p3, (int)grid, c->stream);
+        mark(c, 5);
+      });
+      c->launches++;
+      RF_CUDA(e);
+    }
   } else {
     const int nzh = c->nz / 2 + 1;
     const long long plane = (long long)c->ny * nzh;

@@ -90,9 +90,15 @@ __device__ __forceinline__ cpx<T> twmul(cpx<T> v, const cpx<T>* __restrict__ tw,
 //   storeF(k, c, x)  receives output element k of column/line c
 // `items_c` = number of columns/lines in the tile.  Work items are spread over NT threads.
 // ----------------------------------------------------------------------------------------
-template <typename T, int N, int R1, int R2, int R3, int NT, bool INV, class L, class LoadA, class StoreF>
+struct CtaSync {
+  __device__ __forceinline__ void operator()() const { __syncthreads(); }
+};
+
+template <typename T, int N, int R1, int R2, int R3, int NT, bool INV, class L, class LoadA, class StoreF,
+          class Sync = CtaSync>
 __device__ __forceinline__ void tile_fft(cpx<T>* __restrict__ sm, const cpx<T>* __restrict__ tw,
-                                         int items_c, LoadA&& loadA, StoreF&& storeF) {
+                                         int items_c, LoadA&& loadA, StoreF&& storeF,
+                                         Sync sync = Sync()) {
   static_assert(R1 * R2 * R3 == N, "factorisation");
   constexpr int M = N / R1;
   const int tid = threadIdx.x;
@@ -119,7 +125,7 @@ __device__ __forceinline__ void tile_fft(cpx<T>* __restrict__ sm, const cpx<T>* 
     }
   }
   if constexpr (R2 == 1) return;
-  __syncthreads();
+  sync();
 
   if constexpr (R3 == 1) {
     // ---- step B (final): R2-point DFTs, R2 == M ---------------------------------------
@@ -157,7 +163,7 @@ __device__ __forceinline__ void tile_fft(cpx<T>* __restrict__ sm, const cpx<T>* 
         st_cpx(sm + L::smidx(k1 * M + k2 * M2 + jp, c), x);
       });
     }
-    __syncthreads();
+    sync();
     // ---- step C (final): R3-point DFTs --------------------------------------------------
     for (int w = tid; w < R1 * R2 * items_c; w += NT) {
       int q, c;

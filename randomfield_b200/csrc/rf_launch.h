@@ -3,6 +3,7 @@
 // -DRF_INST_T=... -DRF_INST_N=...) so the build parallelises; rf_api.cu dispatches on N.
 #pragma once
 #include "rf_fast.cuh"
+#include "rf_pipe.cuh"
 
 namespace rf {
 
@@ -13,6 +14,13 @@ struct Launch {
   static int k2(bool inverse, const K2Params<T>& p, int grid, cudaStream_t s);
   static int k3(const K3Params<T>& p, int grid, cudaStream_t s);
   static int k3_lines_per_cta();
+};
+
+// TMA-pipelined kernels (rf_pipe.cuh), float32, one unit per N (rf_pipe_inst.cu)
+template <int N>
+struct PipeLaunch {
+  static int k3p(const pipe::K3PParams& p, int grid, cudaStream_t s);
+  static int k3p_lines_per_tile();
 };
 
 }  // namespace rf

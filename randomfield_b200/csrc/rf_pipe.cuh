@@ -1,0 +1,405 @@
+// rf_pipe.cuh -- persistent, TMA-pipelined versions of the three hot-path kernels (sm_100a).
+//
+// One CTA per SM walks a strided list of tiles.  Warp 8 (one elected lane) is the copy
+// engine driver: it streams tiles between HBM and a two-deep ring of dense shared-memory
+// buffers with bulk-async copies (cp.async.bulk / cp.async.bulk.tensor) and mbarriers; warps
+// 0-7 do the FFT of the tile that has landed while the next one is in flight and the
+// previous one drains.  The FFT itself is the two-step in-register radix engine of
+// rf_fast.cuh, run out of place between the dense buffer and a padded (bank-conflict-free)
+// work buffer, so the dense buffer can be handed to the copy engine as is.
+//
+//   k1p_generate_xfft : modes generated in registers -> x FFT -> TMA store      (4 B/cell)
+//   k2p_strided_fft   : TMA load -> y FFT -> TMA store                          (8 B/cell)
+//   k3p_c2r_lines     : bulk load -> Hermitian unpack + z FFT -> bulk store     (8 B/cell)
+//
+// float32 only; sizes outside the plan table run on the rf_fast.cuh kernels.
+#pragma once
+#include <cuda.h>
+
+#include "rf_fast.cuh"
+
+namespace rf {
+namespace pipe {
+
+constexpr int kConsumers = 256;              // 8 FFT warps
+constexpr int kThreads = kConsumers + 32;    // + 1 copy warp
+constexpr int kTileBytes = 64 * 1024;        // dense tile
+
+// ----------------------------------------------------------------------------------------
+// PTX wrappers
+// ----------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "RF_WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra RF_DONE_%=;\n"
+      "bra RF_WAIT_%=;\n"
+      "RF_DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// generic-proxy writes to shared memory -> visible to the async proxy (bulk copies)
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() {
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+// contiguous global -> shared, completion counted on an mbarrier
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+// contiguous shared -> global, tracked by the issuing thread's bulk async-group
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst),
+               "r"(smem_u32(src)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(m) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0,
+                                            int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, "
+      "%4, %5, %6}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(m),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+// barrier over the consumer warps only (named barrier 1)
+struct ConsumerSync {
+  __device__ __forceinline__ void operator()() const {
+    asm volatile("bar.sync 1, %0;" ::"n"(kConsumers) : "memory");
+  }
+};
+
+// ----------------------------------------------------------------------------------------
+// plans and padded work-buffer layouts
+// ----------------------------------------------------------------------------------------
+// strided axis (k1p, k2p): dense tile [N rows][TZ cols]; work tile has one spare row after
+// every M = N/R1 rows so that the R1 sub-transforms of step B start in different banks
+template <int N>
+struct SPlan;
+#define RF_SPLAN(NN, A, B, TZV)                              \
+  template <>                                                \
+  struct SPlan<NN> {                                         \
+    static constexpr int R1 = A, R2 = B, TZ = TZV, M = NN / A; \
+    static constexpr int kDenseBytes = NN * TZV * 8;         \
+    static constexpr int kWorkBytes = (NN + A) * TZV * 8;    \
+    static constexpr int kBoxRows = NN < 256 ? NN : 256;     \
+  };
+// (M * TZ == kConsumers: every FFT thread owns one (j, column) of step A for the whole run,
+// so its R1-1 step-A twiddles live in registers)
+RF_SPLAN(64, 8, 8, 32)
+RF_SPLAN(128, 16, 8, 32)
+RF_SPLAN(256, 16, 16, 16)
+RF_SPLAN(512, 32, 16, 16)
+RF_SPLAN(1024, 32, 32, 8)
+#undef RF_SPLAN
+
+template <int TZ, int M>
+struct LayoutStridedPad {
+  // element (k1*M + j) of column c
+  __device__ static __forceinline__ int idx2(int k1, int j, int c) { return (k1 * (M + 1) + j) * TZ + c; }
+  __device__ static __forceinline__ void split(int w, int count, int& idx, int& c) {
+    c = w % TZ;
+    idx = w / TZ;
+  }
+};
+
+// contiguous axis (k3p): dense tile [TL lines][H]; work line has one spare element after
+// every M = H/R1 elements
+template <int NZ>
+struct LPlan;
+#define RF_LPLAN2(NN, A, B)                                  \
+  template <>                                                \
+  struct LPlan<NN> {                                         \
+    static constexpr int H = NN / 2, R1 = A, R2 = B, M = H / A; \
+    static constexpr int TL = 8192 / H;                      \
+    static constexpr int WP = H + A;                         \
+    static constexpr int kDenseBytes = TL * H * 8;           \
+    static constexpr int kWorkBytes = TL * WP * 8;           \
+  };
+RF_LPLAN2(64, 8, 4)
+RF_LPLAN2(128, 8, 8)
+RF_LPLAN2(256, 16, 8)
+RF_LPLAN2(512, 16, 16)
+RF_LPLAN2(1024, 16, 32)
+RF_LPLAN2(2048, 32, 32)
+#undef RF_LPLAN2
+
+template <int WP, int M>
+struct LayoutLinesPad {
+  // element (k1*M + j) of line l
+  __device__ static __forceinline__ int idx2(int k1, int j, int l) { return l * WP + k1 * (M + 1) + j; }
+  __device__ static __forceinline__ void split(int w, int count, int& idx, int& l) {
+    idx = w % count;
+    l = w / count;
+  }
+};
+
+// step A: R1-point DFTs over the stride-M samples supplied by loadA, times the step twiddles
+// twr[k1] = W_N^(j*k1) (j is fixed per thread), into the padded work buffer
+template <int N, int R1, class L, class LoadA>
+__device__ __forceinline__ void step_a(cpx<float>* __restrict__ work, int tid, int items_c,
+                                       const cpx<float> (&twr)[R1], LoadA&& loadA) {
+  constexpr int M = N / R1;
+  for (int w = tid; w < M * items_c; w += kConsumers) {
+    int j, c;
+    L::split(w, M, j, c);
+    cpx<float> v[R1];
+    loadA(v, j, c);
+    fft_dif<R1, true>(v);
+    cpx<float>* wp = work + L::idx2(0, j, c);
+    sfor<0, R1>([&](auto ki) {
+      constexpr int k1 = decltype(ki)::value;
+      cpx<float> x = v[brev<R1>(k1)];
+      if constexpr (k1 > 0) x = cmul(x, twr[k1]);
+      st_cpx(wp + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), x);
+    });
+  }
+}
+// step B: R2-point DFTs (R2 == M) out of the work buffer; output element k1 + R1*k2
+template <int N, int R1, class L, class StoreF>
+__device__ __forceinline__ void step_b(const cpx<float>* __restrict__ work, int tid, int items_c,
+                                       StoreF&& storeF) {
+  constexpr int R2 = N / R1;
+  for (int w = tid; w < R1 * items_c; w += kConsumers) {
+    int k1, c;
+    L::split(w, R1, k1, c);
+    cpx<float> v[R2];
+    const cpx<float>* wp = work + L::idx2(k1, 0, c);
+    sfor<0, R2>([&](auto ji) {
+      constexpr int j = decltype(ji)::value;
+      v[j] = ld_cpx(wp + (L::idx2(0, j, 0) - L::idx2(0, 0, 0)));
+    });
+    fft_dif<R2, true>(v);
+    sfor<0, R2>([&](auto ki) {
+      constexpr int k2 = decltype(ki)::value;
+      storeF(k1 + R1 * k2, c, v[brev<R2>(k2)]);
+    });
+  }
+}
+// the step-A twiddles of this thread: W_N^(j*k1), k1 < R1
+template <int R1>
+__device__ __forceinline__ void load_step_twiddles(cpx<float> (&twr)[R1], const cpx<float>* tw, int j) {
+  sfor<0, R1>([&](auto ki) {
+    constexpr int k1 = decltype(ki)::value;
+    twr[k1] = ldg_cpx(tw + j * k1);
+  });
+}
+
+constexpr int kBarBytes = 64;   // full[2], done[2] mbarriers
+
+// ----------------------------------------------------------------------------------------
+// k3p: c2r along the contiguous axis, packed-Nyquist input, in place (see k3_c2r_lines)
+// ----------------------------------------------------------------------------------------
+struct K3PParams {
+  float* buf;              // in: complex [nlines][nz/2]; out: real [nlines][nz] (same bytes)
+  int ntiles;              // nlines / TL
+  const cpx<float>* twH;   // exp(+2 pi i k / (nz/2))
+  const cpx<float>* twN;   // exp(+2 pi i k / nz), k < nz/2
+  const float* zscale;     // optional per-z factor (nz entries) or nullptr
+  double* partials;        // optional [gridDim.x][2] (sum, sum of squares) or nullptr
+};
+
+template <int NZ>
+constexpr int k3p_smem_bytes() {
+  return 2 * LPlan<NZ>::kDenseBytes + LPlan<NZ>::kWorkBytes + kBarBytes;
+}
+
+template <int NZ>
+__global__ void __launch_bounds__(kThreads, 1) k3p_c2r_lines(const K3PParams p) {
+  using P = LPlan<NZ>;
+  constexpr int H = P::H;
+  using L = LayoutLinesPad<P::WP, P::M>;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  cpx<float>* const dense0 = reinterpret_cast<cpx<float>*>(smem_raw);
+  constexpr int kDenseElems = P::kDenseBytes / 8;
+  cpx<float>* const work = reinterpret_cast<cpx<float>*>(smem_raw + 2 * P::kDenseBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + 2 * P::kDenseBytes + P::kWorkBytes);
+  uint64_t* full = bars;       // [2] tile landed in dense[b]
+  uint64_t* done = bars + 2;   // [2] consumers finished writing dense[b]
+  const int tid = threadIdx.x;
+
+  if (tid == 0) {
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    mbar_init(&done[0], kConsumers);
+    mbar_init(&done[1], kConsumers);
+    fence_barrier_init();
+  }
+  __syncthreads();
+
+  const int first = blockIdx.x, step = gridDim.x;
+  char* gbase = reinterpret_cast<char*>(p.buf);
+  constexpr size_t kTile = P::kDenseBytes;
+
+  if (tid >= kConsumers) {
+    // ===== copy warp: one lane drives the bulk copies =====
+    if (tid == kConsumers) {
+      int n = 0;
+      for (int t = first; t < p.ntiles && n < 2; t += step, ++n) {
+        mbar_expect_tx(&full[n], (uint32_t)kTile);
+        bulk_g2s(dense0 + n * kDenseElems, gbase + (size_t)t * kTile, (uint32_t)kTile, &full[n]);
+      }
+      int i = 0;
+      for (int t = first; t < p.ntiles; t += step, ++i) {
+        const int b = i & 1;
+        mbar_wait(&done[b], (i >> 1) & 1);
+        bulk_s2g(gbase + (size_t)t * kTile, dense0 + b * kDenseElems, (uint32_t)kTile);
+        bulk_commit();
+        const int t2 = t + 2 * step;
+        if (t2 < p.ntiles) {
+          bulk_wait_read0();
+          mbar_expect_tx(&full[b], (uint32_t)kTile);
+          bulk_g2s(dense0 + b * kDenseElems, gbase + (size_t)t2 * kTile, (uint32_t)kTile, &full[b]);
+        }
+      }
+      bulk_wait0();
+    }
+    return;
+  }
+
+  // ===== FFT warps =====
+  double s1 = 0.0, s2 = 0.0;
+  const float* zs = p.zscale;
+  // per-thread constants: the unpack pair index k, its twiddle, and the step-A twiddles
+  static_assert(kConsumers % (H / 2) == 0 || (H / 2) % kConsumers == 0, "unpack mapping");
+  constexpr int kPairsPerThread = (H / 2 + kConsumers - 1) / kConsumers;   // per line
+  cpx<float> twu[kPairsPerThread];
+  sfor<0, kPairsPerThread>([&](auto qi) {
+    constexpr int q = decltype(qi)::value;
+    twu[q] = ldg_cpx(p.twN + (tid + q * kConsumers) % (H / 2));
+  });
+  cpx<float> twr[P::R1];
+  load_step_twiddles<P::R1>(twr, p.twH, tid % P::M);
+  int i = 0;
+  for (int t = first; t < p.ntiles; t += step, ++i) {
+    const int b = i & 1;
+    cpx<float>* const D = dense0 + b * kDenseElems;
+    mbar_wait(&full[b], (i >> 1) & 1);
+
+    // Hermitian unpack in place: Z[k] = E[k] + i*O[k] for the pair (k, H-k)
+    if constexpr (H / 2 >= kConsumers) {
+      // thread owns pairs k = tid + q*kConsumers of every line
+#pragma unroll 2
+      for (int l = 0; l < P::TL; ++l) {
+        cpx<float>* Lp = D + l * H;
+        sfor<0, kPairsPerThread>([&](auto qi) {
+          constexpr int q = decltype(qi)::value;
+          const int k = tid + q * kConsumers;
+          if (q == 0 && k == 0) {
+            cpx<float> a = Lp[0], m = Lp[H / 2];
+            Lp[0] = {a.x + a.y, a.x - a.y};          // X[0], X[H] are real
+            Lp[H / 2] = {2.f * m.x, -2.f * m.y};
+          } else {
+            cpx<float> a = Lp[k], c = Lp[H - k];
+            cpx<float> e = {a.x + c.x, a.y - c.y};   // X[k] + conj(X[H-k])
+            cpx<float> d = {a.x - c.x, a.y + c.y};   // X[k] - conj(X[H-k])
+            cpx<float> o = cmul(d, twu[q]);          // * exp(+2 pi i k / NZ)
+            Lp[k] = {e.x - o.y, e.y + o.x};
+            Lp[H - k] = {e.x + o.y, o.x - e.y};
+          }
+        });
+      }
+    } else {
+      // several lines per sweep: thread owns pair k = tid % (H/2) of lines tid/(H/2) + ...
+      constexpr int kLinesPerSweep = kConsumers / (H / 2);
+      const int k = tid % (H / 2);
+      for (int l = tid / (H / 2); l < P::TL; l += kLinesPerSweep) {
+        cpx<float>* Lp = D + l * H;
+        if (k == 0) {
+          cpx<float> a = Lp[0], m = Lp[H / 2];
+          Lp[0] = {a.x + a.y, a.x - a.y};
+          Lp[H / 2] = {2.f * m.x, -2.f * m.y};
+        } else {
+          cpx<float> a = Lp[k], c = Lp[H - k];
+          cpx<float> e = {a.x + c.x, a.y - c.y};
+          cpx<float> d = {a.x - c.x, a.y + c.y};
+          cpx<float> o = cmul(d, twu[0]);
+          Lp[k] = {e.x - o.y, e.y + o.x};
+          Lp[H - k] = {e.x + o.y, o.x - e.y};
+        }
+      }
+    }
+    ConsumerSync()();
+
+    float a1 = 0.f, a2 = 0.f;
+    step_a<H, P::R1, L>(work, tid, P::TL, twr, [&](cpx<float>(&v)[P::R1], int j, int l) {
+      const cpx<float>* Lp = D + l * H + j;
+      sfor<0, P::R1>([&](auto mi) {
+        constexpr int m = decltype(mi)::value;
+        v[m] = ld_cpx(Lp + P::M * m);
+      });
+    });
+    ConsumerSync()();
+    step_b<H, P::R1, L>(work, tid, P::TL, [&](int k, int l, cpx<float> x) {
+      a1 += x.x + x.y;
+      a2 = fmaf(x.x, x.x, fmaf(x.y, x.y, a2));
+      if (zs) {
+        float2 z = __ldg(reinterpret_cast<const float2*>(zs) + k);
+        x.x *= z.x;
+        x.y *= z.y;
+      }
+      st_cpx(D + l * H + k, x);
+    });
+    s1 += (double)a1;
+    s2 += (double)a2;
+    fence_proxy_async();
+    mbar_arrive(&done[b]);
+  }
+
+  if (p.partials) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    __shared__ double red[2][kConsumers / 32];
+    const int wid = tid >> 5, lane = tid & 31;
+    if (lane == 0) { red[0][wid] = s1; red[1][wid] = s2; }
+    ConsumerSync()();
+    if (tid == 0) {
+      double t1 = 0, t2 = 0;
+      for (int q = 0; q < kConsumers / 32; ++q) { t1 += red[0][q]; t2 += red[1][q]; }
+      p.partials[2 * (size_t)blockIdx.x] = t1;
+      p.partials[2 * (size_t)blockIdx.x + 1] = t2;
+    }
+  }
+}
+
+// @@PIPE_END@@
+}  // namespace pipe
+}  // namespace rf

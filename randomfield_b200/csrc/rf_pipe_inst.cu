@@ -1,0 +1,31 @@
+// rf_pipe_inst.cu -- one instantiation unit of the TMA-pipelined kernels: compile with
+//   -DRF_PIPE_N=<power of two in [64, 2048]>
+#include "rf_launch.h"
+
+#ifndef RF_PIPE_N
+#error "define RF_PIPE_N"
+#endif
+
+namespace rf {
+
+constexpr int N = RF_PIPE_N;
+
+template <class K>
+static int set_smem_pipe(K kernel, int bytes) {
+  return (int)cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
+template <>
+int PipeLaunch<N>::k3p(const pipe::K3PParams& p, int grid, cudaStream_t s) {
+  constexpr int smem = pipe::k3p_smem_bytes<N>();
+  int e;
+  if ((e = set_smem_pipe(pipe::k3p_c2r_lines<N>, smem))) return e;
+  pipe::k3p_c2r_lines<N><<<grid, pipe::kThreads, smem, s>>>(p);
+  return (int)cudaGetLastError();
+}
+template <>
+int PipeLaunch<N>::k3p_lines_per_tile() {
+  return pipe::LPlan<N>::TL;
+}
+
+}  // namespace rf
