@@ -350,6 +350,40 @@ extern "C" int rf_set_noise(rf_ctx* c, const double* host_noise) {
   return RF_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// TMA tensor maps (driver entry point fetched through the runtime; no -lcuda link)
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPointByVersion("cuTensorMapEncodeTiled", &p, 12000, cudaEnableDefault, &q) ==
+            cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+// float32 tensor of `rank` dims (fastest first); strides[d-1] = byte stride of dim d
+static int make_tensor_map(CUtensorMap* m, void* base, int rank, const uint64_t* dims,
+                           const uint64_t* strides, const uint32_t* box) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return fail(RF_ERR_CUDA, "cuTensorMapEncodeTiled is not available");
+  cuuint64_t gd[5], gs[4];
+  cuuint32_t bx[5], es[5];
+  for (int d = 0; d < rank; ++d) { gd[d] = dims[d]; bx[d] = box[d]; es[d] = 1; }
+  for (int d = 0; d + 1 < rank; ++d) gs[d] = strides[d];
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, base, gd, gs, bx, es,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(RF_ERR_CUDA, "cuTensorMapEncodeTiled failed: " + std::to_string((int)r));
+  return RF_OK;
+}
+
 template <typename T>
 static ModeGeom<T> make_geom(rf_ctx* c, uint64_t seed, int potential) {
   ModeGeom<T> g;
@@ -395,6 +429,16 @@ static int ensure_partials(rf_ctx* c, long long n) {
     case 512: { constexpr int NN = 512; __VA_ARGS__; } break;  \
     case 1024: { constexpr int NN = 1024; __VA_ARGS__; } break;\
     case 2048: { constexpr int NN = 2048; __VA_ARGS__; } break;\
+    default: return fail(RF_ERR_ARG, "size not compiled");\
+  }
+
+#define RF_DISPATCH_PIPE1K(N_, ...)                     \
+  switch (N_) {                                         \
+    case 64: { constexpr int NN = 64; __VA_ARGS__; } break;    \
+    case 128: { constexpr int NN = 128; __VA_ARGS__; } break;  \
+    case 256: { constexpr int NN = 256; __VA_ARGS__; } break;  \
+    case 512: { constexpr int NN = 512; __VA_ARGS__; } break;  \
+    case 1024: { constexpr int NN = 1024; __VA_ARGS__; } break;\
     default: return fail(RF_ERR_ARG, "size not compiled");\
   }
 
@@ -517,14 +561,50 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
       p2.rows_per_src = c->ny;
     }
     int e = 0;
+    bool done2 = false;
+    if constexpr (std::is_same<T, float>::value) {
+      if (c->pipe && c->ny <= 1024) {
+        pipe::K2PParams q;
+        q.tw = (const cpx<float>*)c->tw_y;
+        q.rows_per_src = p2.rows_per_src;
+        CUtensorMap min, mout;
+        RF_DISPATCH_PIPE1K(c->ny, {
+          const int tz = PipeLaunch<NN>::tile_cols();
+          q.ztiles = nzc / tz;
+          q.ntiles = c->nxl * q.ztiles;
+          q.box_rows = std::min(PipeLaunch<NN>::box_rows(), q.rows_per_src);
+          const int nsrc = c->ny / q.rows_per_src;
+          uint64_t din[4] = {(uint64_t)2 * nzc, (uint64_t)q.rows_per_src, (uint64_t)c->nxl, (uint64_t)nsrc};
+          uint64_t sin[3] = {(uint64_t)p2.in_row * 8, (uint64_t)p2.in_outer * 8,
+                             (uint64_t)(nsrc > 1 ? p2.in_src : p2.in_outer * c->nxl) * 8};
+          uint32_t bin[4] = {(uint32_t)2 * tz, (uint32_t)q.box_rows, 1, 1};
+          int e2 = make_tensor_map(&min, (void*)p2.in, 4, din, sin, bin);
+          if (e2) return e2;
+          uint64_t dout[3] = {(uint64_t)2 * nzc, (uint64_t)c->ny, (uint64_t)c->nxl};
+          uint64_t sout[2] = {(uint64_t)p2.out_row * 8, (uint64_t)p2.out_outer * 8};
+          uint32_t bout[3] = {(uint32_t)2 * tz, (uint32_t)PipeLaunch<NN>::box_rows(), 1};
+          e2 = make_tensor_map(&mout, (void*)p2.out, 3, dout, sout, bout);
+          if (e2) return e2;
+          int grid = std::min(q.ntiles, c->num_sms);
+          mark(c, 2);
+          e = PipeLaunch<NN>::k2p(min, mout, q, grid, c->stream);
+          mark(c, 3);
+        });
+        c->launches++;
+        RF_CUDA(e);
+        done2 = true;
+      }
+    }
+    if (!done2) {
     RF_DISPATCH_N(c->ny, {
-      int grid = c->nxl * (nzc / FftPlan<T, NN>::TZ);
-      mark(c, 2);
-      e = Launch<T, NN>::k2(true, p2, grid, c->stream);
-      mark(c, 3);
-    });
-    c->launches++;
-    RF_CUDA(e);
+        int grid = c->nxl * (nzc / FftPlan<T, NN>::TZ);
+        mark(c, 2);
+        e = Launch<T, NN>::k2(true, p2, grid, c->stream);
+        mark(c, 3);
+      });
+      c->launches++;
+      RF_CUDA(e);
+    }
     bool done3 = false;
     if constexpr (std::is_same<T, float>::value) {
       if (c->pipe && c->nz <= 2048) {

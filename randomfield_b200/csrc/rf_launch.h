@@ -21,6 +21,11 @@ template <int N>
 struct PipeLaunch {
   static int k3p(const pipe::K3PParams& p, int grid, cudaStream_t s);
   static int k3p_lines_per_tile();
+  // N <= 1024 only
+  static int k2p(const CUtensorMap& in, const CUtensorMap& out, const pipe::K2PParams& p, int grid,
+                 cudaStream_t s);
+  static int tile_cols();   // TZ
+  static int box_rows();    // rows per TMA box of the store map
 };
 
 }  // namespace rf

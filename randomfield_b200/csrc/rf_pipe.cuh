@@ -400,6 +400,110 @@ __global__ void __launch_bounds__(kThreads, 1) k3p_c2r_lines(const K3PParams p) 
   }
 }
 
+// ----------------------------------------------------------------------------------------
+// k2p: inverse FFT along a strided axis.  Tile = [N rows][TZ columns] of one outer index.
+//   load map  (4-D): (2*ncols floats, rows per source block, outer, source block)
+//   store map (3-D): (2*ncols floats, N rows, outer)
+// Single GPU: both maps describe the field buffer (in place; a tile reads and writes the
+// same cells).  Slab-decomposed: the load map describes the all-to-all receive buffer
+// [src][nx/G][ny/G][ncols], whose source blocks each hold ny/G rows of every line.
+// ----------------------------------------------------------------------------------------
+struct K2PParams {
+  const cpx<float>* tw;    // exp(+2 pi i k / N)
+  int ntiles;              // outer * ztiles
+  int ztiles;              // ncols / TZ
+  int rows_per_src;        // rows of a line held by one source block (N when single GPU)
+  int box_rows;            // rows per TMA box = min(256, rows_per_src)
+};
+
+template <int N>
+constexpr int k2p_smem_bytes() {
+  return 2 * SPlan<N>::kDenseBytes + SPlan<N>::kWorkBytes + kBarBytes;
+}
+
+template <int N>
+__global__ void __launch_bounds__(kThreads, 1)
+k2p_strided_fft(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_out,
+                const K2PParams p) {
+  using P = SPlan<N>;
+  using L = LayoutStridedPad<P::TZ, P::M>;
+  static_assert(P::M * P::TZ == kConsumers, "one step-A item per thread");
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  cpx<float>* const dense0 = reinterpret_cast<cpx<float>*>(smem_raw);
+  constexpr int kDenseElems = P::kDenseBytes / 8;
+  cpx<float>* const work = reinterpret_cast<cpx<float>*>(smem_raw + 2 * P::kDenseBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + 2 * P::kDenseBytes + P::kWorkBytes);
+  uint64_t* full = bars;
+  uint64_t* done = bars + 2;
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    mbar_init(&done[0], kConsumers);
+    mbar_init(&done[1], kConsumers);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  const int first = blockIdx.x, step = gridDim.x;
+
+  if (tid >= kConsumers) {
+    if (tid == kConsumers) {
+      tma_prefetch_desc(&map_in);
+      tma_prefetch_desc(&map_out);
+      auto load_tile = [&](int t, int b) {
+        const int o = t / p.ztiles, z0 = (t % p.ztiles) * P::TZ;
+        mbar_expect_tx(&full[b], (uint32_t)P::kDenseBytes);
+        for (int r0 = 0; r0 < N; r0 += p.box_rows) {
+          const int src = r0 / p.rows_per_src, rl = r0 - src * p.rows_per_src;
+          tma_load_4d(dense0 + b * kDenseElems + r0 * P::TZ, &map_in, &full[b], 2 * z0, rl, o, src);
+        }
+      };
+      int n = 0;
+      for (int t = first; t < p.ntiles && n < 2; t += step, ++n) load_tile(t, n);
+      int i = 0;
+      for (int t = first; t < p.ntiles; t += step, ++i) {
+        const int b = i & 1;
+        mbar_wait(&done[b], (i >> 1) & 1);
+        const int o = t / p.ztiles, z0 = (t % p.ztiles) * P::TZ;
+        for (int r0 = 0; r0 < N; r0 += P::kBoxRows)
+          tma_store_3d(&map_out, dense0 + b * kDenseElems + r0 * P::TZ, 2 * z0, r0, o);
+        bulk_commit();
+        const int t2 = t + 2 * step;
+        if (t2 < p.ntiles) {
+          bulk_wait_read0();
+          load_tile(t2, b);
+        }
+      }
+      bulk_wait0();
+    }
+    return;
+  }
+
+  const int c = tid % P::TZ, j = tid / P::TZ;
+  cpx<float> twr[P::R1];
+  load_step_twiddles<P::R1>(twr, p.tw, j);
+  int i = 0;
+  for (int t = first; t < p.ntiles; t += step, ++i) {
+    const int b = i & 1;
+    cpx<float>* const D = dense0 + b * kDenseElems;
+    mbar_wait(&full[b], (i >> 1) & 1);
+    step_a<N, P::R1, L>(work, tid, P::TZ, twr, [&](cpx<float>(&v)[P::R1], int jj, int cc) {
+      const cpx<float>* Dp = D + jj * P::TZ + cc;
+      sfor<0, P::R1>([&](auto mi) {
+        constexpr int m = decltype(mi)::value;
+        v[m] = ld_cpx(Dp + P::M * m * P::TZ);
+      });
+    });
+    ConsumerSync()();
+    step_b<N, P::R1, L>(work, tid, P::TZ, [&](int k, int cc, cpx<float> x) { st_cpx(D + k * P::TZ + cc, x); });
+    fence_proxy_async();
+    mbar_arrive(&done[b]);
+    // the next tile's step A overwrites the work buffer: everyone must be out of step B
+    ConsumerSync()();
+  }
+  (void)c;
+}
+
 // @@PIPE_END@@
 }  // namespace pipe
 }  // namespace rf

@@ -28,4 +28,24 @@ int PipeLaunch<N>::k3p_lines_per_tile() {
   return pipe::LPlan<N>::TL;
 }
 
+#if RF_PIPE_N <= 1024
+template <>
+int PipeLaunch<N>::k2p(const CUtensorMap& in, const CUtensorMap& out, const pipe::K2PParams& p, int grid,
+                       cudaStream_t s) {
+  constexpr int smem = pipe::k2p_smem_bytes<N>();
+  int e;
+  if ((e = set_smem_pipe(pipe::k2p_strided_fft<N>, smem))) return e;
+  pipe::k2p_strided_fft<N><<<grid, pipe::kThreads, smem, s>>>(in, out, p);
+  return (int)cudaGetLastError();
+}
+template <>
+int PipeLaunch<N>::tile_cols() {
+  return pipe::SPlan<N>::TZ;
+}
+template <>
+int PipeLaunch<N>::box_rows() {
+  return pipe::SPlan<N>::kBoxRows;
+}
+#endif
+
 }  // namespace rf
