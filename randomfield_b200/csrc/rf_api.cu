@@ -55,6 +55,9 @@ struct rf_ctx {
   // sigma table
   void* knots = nullptr;
   void* cells = nullptr;
+  void* hinge = nullptr;     // float4 per cell (f32 only)
+  void* plane = nullptr;     // [nx][nyl] packed iz = 0 / nz/2 column for k1p
+  bool hinge_ok = false;     // every non-zero mode of the grid falls in a hinge-valid cell
   int ntab = 0, lut_n = 0, lut_base = 0, lut_shift = 0;
   double spacing = 0.0;
   bool have_power = false;
@@ -149,7 +152,7 @@ extern "C" int rf_destroy(rf_ctx* c) {
   if (!c) return RF_OK;
   cudaStreamSynchronize(c->stream);
   void* ptrs[] = {c->field, c->recv, c->partials, c->stats_dev, c->tw_x, c->tw_y, c->tw_z,
-                  c->tw_zh, c->knots, c->cells, c->noise, c->zs_dev, c->da_dev, c->db_dev};
+                  c->tw_zh, c->knots, c->cells, c->hinge, c->plane, c->noise, c->zs_dev, c->da_dev, c->db_dev};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -307,9 +310,53 @@ static int build_table(rf_ctx* c, int n, const double* k, const double* sigma) {
     }
     cells[e] = s;
   }
+  // hinge form of the same cells (float path): segment below the knot + slope change at it
+  std::vector<float> hinge;
+  bool hinge_ok = false;
+  if (std::is_same<T, float>::value) {
+    hinge.assign((size_t)4 * ln, 0.f);
+    std::vector<char> valid(ln, 0);
+    next = 0;
+    for (int e = 1; e < ln - 1; ++e) {
+      const int id = base + e;
+      while (next < n && cell_of(kn[next].ksq, shift) < id) ++next;
+      int cnt = 0;
+      while (next + cnt < n && cell_of(kn[next + cnt].ksq, shift) == id) ++cnt;
+      const int jlo = next - 1;
+      if (jlo < 0 || cnt > 1 || next + cnt >= n) continue;   // touches the table's ends, or 2+ knots
+      float c0, c1;
+      {
+        T a, b;
+        seg_coef(jlo, a, b);
+        c0 = (float)a; c1 = (float)b;
+      }
+      float lt = 0.f, d = 0.f;
+      if (cnt == 1) { lt = (float)l2[next]; d = (float)(slope[next] - slope[jlo]); }
+      hinge[4 * e + 0] = c0; hinge[4 * e + 1] = c1; hinge[4 * e + 2] = lt; hinge[4 * e + 3] = d;
+      valid[e] = 1;
+    }
+    // grid modes: smallest non-zero k^2 and largest k^2 (with a cell of margin either side)
+    const double two_pi = 6.283185307179586476925286766559;
+    double kmin2 = 1e300, kmax2 = 0;
+    for (int n_ax : {c->nx, c->ny, c->nz}) {
+      double k0 = two_pi / ((double)n_ax * c->spacing);
+      kmin2 = std::min(kmin2, k0 * k0);
+      kmax2 += (0.5 * n_ax * k0) * (0.5 * n_ax * k0);
+    }
+    const int elo = cell_of((T)kmin2, shift) - base - 1, ehi = cell_of((T)kmax2, shift) - base + 1;
+    hinge_ok = elo >= 1 && ehi <= ln - 2;
+    for (int e = std::max(elo, 1); hinge_ok && e <= ehi; ++e) hinge_ok = valid[e] != 0;
+  }
   if (c->knots) cudaFree(c->knots);
   if (c->cells) cudaFree(c->cells);
-  c->knots = nullptr; c->cells = nullptr;
+  if (c->hinge) cudaFree(c->hinge);
+  c->knots = nullptr; c->cells = nullptr; c->hinge = nullptr;
+  c->hinge_ok = false;
+  if (!hinge.empty()) {
+    RF_CUDA(cudaMalloc(&c->hinge, sizeof(float) * hinge.size()));
+    RF_CUDA(cudaMemcpy(c->hinge, hinge.data(), sizeof(float) * hinge.size(), cudaMemcpyHostToDevice));
+    c->hinge_ok = hinge_ok;
+  }
   RF_CUDA(cudaMalloc(&c->knots, sizeof(knot<T>) * n));
   RF_CUDA(cudaMalloc(&c->cells, sizeof(sigcell<T>) * ln));
   // the table may be replaced while earlier work is still queued on the stream
@@ -402,7 +449,7 @@ static ModeGeom<T> make_geom(rf_ctx* c, uint64_t seed, int potential) {
 template <typename T>
 static SigmaTable<T> make_tab(rf_ctx* c) {
   SigmaTable<T> t;
-  t.knots = (const knot<T>*)c->knots; t.cells = (const sigcell<T>*)c->cells;
+  t.knots = (const knot<T>*)c->knots; t.cells = (const sigcell<T>*)c->cells; t.hinge = c->hinge;
   t.n = c->ntab; t.lut_n = c->lut_n; t.lut_base = c->lut_base; t.shift = c->lut_shift;
   return t;
 }
@@ -484,6 +531,42 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
   SigmaTable<T> tab = make_tab<T>(c);
   c->field_is_real = false;
   c->stats_valid = false;
+  if constexpr (std::is_same<T, float>::value) {
+    if (c->pipe && c->nx <= 1024 && c->hinge_ok) {
+      pipe::K1PParams q;
+      q.geom = g; q.tab = tab; q.tw = (const cpx<float>*)c->tw_x;
+      q.ny_local = c->nyl; q.y0 = c->rank * c->nyl;
+      const int nzc = c->nz / 2;
+      if (!c->plane) RF_CUDA(cudaMalloc(&c->plane, sizeof(cpx<float>) * (size_t)c->nx * c->nyl));
+      {
+        const int total = c->nx * c->nyl;
+        gen_packed_plane_kernel<float><<<std::min((total + 127) / 128, 148 * 16), 128, 0, c->stream>>>(
+            g, tab, (cpx<float>*)c->plane, c->rank * c->nyl, c->nyl);
+        c->launches++;
+        RF_CUDA(cudaGetLastError());
+      }
+      q.plane = (const cpx<float>*)c->plane;
+      int e = 0;
+      CUtensorMap mout;
+      RF_DISPATCH_PIPE1K(c->nx, {
+        const int tz = PipeLaunch<NN>::tile_cols();
+        q.ztiles = nzc / tz;
+        q.ntiles = c->nyl * q.ztiles;
+        uint64_t dout[3] = {(uint64_t)2 * nzc, (uint64_t)c->nyl, (uint64_t)c->nx};
+        uint64_t sout[2] = {(uint64_t)nzc * 8, (uint64_t)c->nyl * nzc * 8};
+        uint32_t bout[3] = {(uint32_t)2 * tz, 1, (uint32_t)PipeLaunch<NN>::box_rows()};
+        int e2 = make_tensor_map(&mout, c->field, 3, dout, sout, bout);
+        if (e2) return e2;
+        int grid = std::min(q.ntiles, c->num_sms);
+        mark(c, 0);
+        e = PipeLaunch<NN>::k1p(c->noise != nullptr, potential != 0, mout, q, grid, c->stream);
+        mark(c, 1);
+      });
+      c->launches++;
+      RF_CUDA(e);
+      return RF_OK;
+    }
+  }
   if (c->fast) {
     K1Params<T> p;
     p.geom = g; p.tab = tab; p.out = (cpx<T>*)c->field; p.tw = (const cpx<T>*)c->tw_x;

@@ -222,6 +222,7 @@ template <typename T>
 struct SigmaTable {
   const knot<T>* knots;     // n entries
   const sigcell<T>* cells;  // lut_n entries; first and last are all-zero sentinels
+  const void* hinge;        // float4 {c0, c1, lt, d} per cell (float path only), see sigma_hinge
   int n;
   int lut_n;
   int lut_base;             // cell id of cells[0]
@@ -274,6 +275,19 @@ __device__ __forceinline__ T sigma_eval(const SigmaTable<T>& tab, T ksq, int* bi
   if (bin_out) *bin_out = (int)bin_a + (up ? 1 : 0);
   const T c0 = up ? c0b : c0a, c1 = up ? c1b : c1a;
   return c0 + c1 * rf_log2(fmax(ksq, rf_tiny((T)0)));
+}
+
+// Branch-free single-load evaluation used by the fused generator:
+//   sigma = c0 + c1*lg + d*max(lg - lt, 0),  lg = log2(k^2)
+// i.e. the segment below the cell's knot plus a hinge of slope change d at the knot (log2 of
+// the knot = lt; d = 0 when the cell holds no knot).  Valid for every cell that lies strictly
+// between the first and the last knot's cells and holds at most one knot; the host only
+// enables kernels that use it when all non-zero modes of the grid fall in such cells.
+__device__ __forceinline__ float sigma_hinge(const SigmaTable<float>& tab, float ksq) {
+  const int c = min(max(coarse_cell(ksq, tab.shift) - tab.lut_base, 0), tab.lut_n - 1);
+  const float4 h = __ldg(reinterpret_cast<const float4*>(tab.hinge) + c);
+  const float lg = __log2f(ksq);
+  return fmaf(h.w, fmaxf(lg - h.z, 0.f), fmaf(h.y, lg, h.x));
 }
 
 template <typename T>

@@ -33,6 +33,24 @@ __global__ void gen_kspace_public_kernel(ModeGeom<T> g, SigmaTable<T> tab, cpx<T
 }
 
 // ----------------------------------------------------------------------------------------
+// The packed-Nyquist column of the internal layout: out[ix][iy_local] = P0 + i*PN where P0 / PN
+// are the symmetrised modes on the planes iz = 0 and iz = nz/2 (internal normalisation).
+// 2*nx*ny modes; the fused generator (k1p) reads this instead of evaluating the Hermitian
+// rule inside its hot loop.
+// ----------------------------------------------------------------------------------------
+template <typename T>
+__global__ void gen_packed_plane_kernel(ModeGeom<T> g, SigmaTable<T> tab, cpx<T>* out, int y0,
+                                        int ny_local) {
+  const int total = g.nx * ny_local;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int iyl = i % ny_local, ix = i / ny_local;
+    cpx<T> a = sym_mode(g, tab, ix, y0 + iyl, 0);
+    cpx<T> b = sym_mode(g, tab, ix, y0 + iyl, g.nz / 2);
+    out[i] = {a.x - b.y, a.y + b.x};
+  }
+}
+
+// ----------------------------------------------------------------------------------------
 // any-length FFT of one line held in shared memory.  x holds the input, y is scratch,
 // tw holds exp(+2 pi i k / n).  Returns the buffer that holds the result.
 // Power-of-two lengths: Stockham radix-2; otherwise a direct O(n^2) DFT.

@@ -24,6 +24,7 @@ struct PipeLaunch {
   // N <= 1024 only
   static int k2p(const CUtensorMap& in, const CUtensorMap& out, const pipe::K2PParams& p, int grid,
                  cudaStream_t s);
+  static int k1p(bool injected, bool potential, const CUtensorMap& out, const pipe::K1PParams& p, int grid, cudaStream_t s);
   static int tile_cols();   // TZ
   static int box_rows();    // rows per TMA box of the store map
 };

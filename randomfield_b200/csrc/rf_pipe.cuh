@@ -504,6 +504,112 @@ k2p_strided_fft(const __grid_constant__ CUtensorMap map_in, const __grid_constan
   (void)c;
 }
 
+// ----------------------------------------------------------------------------------------
+// k1p: modes generated in registers (Philox + Box-Muller + sigma(k) + Hermitian pairing),
+// inverse FFT along x, TMA store.  Tile = [NX rows][TZ columns] of one local y index.
+//   store map (3-D): (2*ncols floats, ny_local, NX)
+// ----------------------------------------------------------------------------------------
+struct K1PParams {
+  ModeGeom<float> geom;
+  SigmaTable<float> tab;
+  const cpx<float>* tw;    // exp(+2 pi i k / nx)
+  const cpx<float>* plane; // [nx][ny_local] packed iz = 0 / nz/2 column (gen_packed_plane_kernel)
+  int ny_local, y0;        // y-slab owned by this rank; y0 = first global iy
+  int ntiles, ztiles;      // ny_local * ztiles, (nz/2) / TZ
+};
+
+template <int NX>
+constexpr int k1p_smem_bytes() {
+  return 2 * SPlan<NX>::kDenseBytes + SPlan<NX>::kWorkBytes + kBarBytes;
+}
+
+// No copy warp here: the kernel is issue-bound, there is nothing to load, and 8 warps (2 per
+// scheduler) may use up to 255 registers where 9 may use 168.  Thread 0 issues the tile's TMA
+// stores after step B and, two tiles later, checks that they have drained the buffer.
+template <int NX, bool INJ, bool POT>
+__global__ void __launch_bounds__(kConsumers, 1)
+k1p_generate_xfft(const __grid_constant__ CUtensorMap map_out, const K1PParams p) {
+  using P = SPlan<NX>;
+  using L = LayoutStridedPad<P::TZ, P::M>;
+  static_assert(P::M * P::TZ == kConsumers, "one step-A item per thread");
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  cpx<float>* const dense0 = reinterpret_cast<cpx<float>*>(smem_raw);
+  constexpr int kDenseElems = P::kDenseBytes / 8;
+  cpx<float>* const work = reinterpret_cast<cpx<float>*>(smem_raw + 2 * P::kDenseBytes);
+  const int tid = threadIdx.x;
+  const int first = blockIdx.x, step = gridDim.x;
+  if (tid == 0) tma_prefetch_desc(&map_out);
+
+  const ModeGeom<float>& g = p.geom;
+  const int c = tid % P::TZ, j = tid / P::TZ;
+  const int nzh = g.nz / 2 + 1;
+  cpx<float> twr[P::R1];
+  load_step_twiddles<P::R1>(twr, p.tw, j);
+  const float fj = (float)j;
+  const uint64_t dq = (uint64_t)P::M * g.ny * nzh;   // Philox counter step between m and m+1
+  int i = 0;
+  for (int t = first; t < p.ntiles; t += step, ++i) {
+    const int b = i & 1;
+    cpx<float>* const D = dense0 + b * kDenseElems;
+    const int iyl = t / p.ztiles, z0 = (t % p.ztiles) * P::TZ;
+    const int iy = p.y0 + iyl;
+
+    step_a<NX, P::R1, L>(work, tid, P::TZ, twr, [&](cpx<float>(&v)[P::R1], int jj, int cc) {
+      const int iz = z0 + cc;
+      if (iz == 0) {
+        // packed column (iz=0 plane) + i*(iz=nz/2 plane): precomputed by gen_packed_plane_kernel
+        const cpx<float>* pp = p.plane + (size_t)jj * p.ny_local + iyl;
+        sfor<0, P::R1>([&](auto mi) {
+          constexpr int m = decltype(mi)::value;
+          v[m] = ldg_cpx(pp + (size_t)(P::M * m) * p.ny_local);
+        });
+      } else if constexpr (INJ) {
+        sfor<0, P::R1>([&](auto mi) {
+          constexpr int m = decltype(mi)::value;
+          v[m] = raw_mode(g, p.tab, jj + P::M * m, iy, iz);
+        });
+      } else {
+        // k^2 = fma(jx^2, k0x2, fma(jy^2, k0y2, jz^2*k0z2)): the inner part is per tile
+        const float ksq_yz = ksq_canon(0.f, mode_sq<float>(iy, g.ny), mode_sq<float>(iz, g.nz), g.k0x2,
+                                       g.k0y2, g.k0z2);
+        const uint64_t q0 = ((uint64_t)jj * g.ny + iy) * nzh + iz;
+        sfor<0, P::R1 / 2>([&](auto mi) {
+          constexpr int m = decltype(mi)::value;
+          // ix = j + M*m < nx/2 and its partner ix + nx/2 (signed mode ix - nx/2) share a counter
+          const float f1 = fj + (float)(P::M * m), f2 = f1 - (float)(NX / 2);
+          const float ks1 = __fmaf_rn(f1 * f1, g.k0x2, ksq_yz);
+          const float ks2 = __fmaf_rn(f2 * f2, g.k0x2, ksq_yz);
+          float s1 = sigma_hinge(p.tab, ks1), s2 = sigma_hinge(p.tab, ks2);
+          if constexpr (POT) {
+            s1 = __fdividef(s1, ks1);   // k^2 > 0 off the iz = 0 plane
+            s2 = __fdividef(s2, ks2);
+          }
+          const uint64_t q = q0 + (uint64_t)m * dq;
+          philox_out o = philox4x32_10((uint32_t)q, (uint32_t)(q >> 32), 0u, 0u, g.key0, g.key1);
+          cpx<float> n1 = box_muller<float>(o.w[0], o.w[1]);
+          cpx<float> n2 = box_muller<float>(o.w[2], o.w[3]);
+          v[m] = {s1 * n1.x, s1 * n1.y};
+          v[m + P::R1 / 2] = {s2 * n2.x, s2 * n2.y};
+        });
+      }
+    });
+    // buffer b was last stored from two tiles ago: at most the previous tile's store may
+    // still be reading shared memory
+    if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+    __syncthreads();
+    step_b<NX, P::R1, L>(work, tid, P::TZ, [&](int k, int cc, cpx<float> x) { st_cpx(D + k * P::TZ + cc, x); });
+    fence_proxy_async();
+    __syncthreads();
+    if (tid == 0) {
+      for (int r0 = 0; r0 < NX; r0 += P::kBoxRows)
+        tma_store_3d(&map_out, D + r0 * P::TZ, 2 * z0, iyl, r0);
+      bulk_commit();
+    }
+  }
+  if (tid == 0) bulk_wait0();
+  (void)c;
+}
+
 // @@PIPE_END@@
 }  // namespace pipe
 }  // namespace rf
