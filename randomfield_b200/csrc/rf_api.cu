@@ -668,6 +668,7 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
           uint32_t bout[3] = {(uint32_t)2 * tz, (uint32_t)PipeLaunch<NN>::box_rows(), 1};
           e2 = make_tensor_map(&mout, (void*)p2.out, 3, dout, sout, bout);
           if (e2) return e2;
+          q.tile0 = 0;
           int grid = std::min(q.ntiles, c->num_sms);
           mark(c, 2);
           e = PipeLaunch<NN>::k2p(min, mout, q, grid, c->stream);
@@ -700,6 +701,7 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
         RF_DISPATCH_PIPE(c->nz, {
           const long long nlines = (long long)c->nxl * c->ny;
           q.ntiles = (int)(nlines / PipeLaunch<NN>::k3p_lines_per_tile());
+          q.tile0 = 0;
           int grid = std::min(q.ntiles, c->num_sms);
           if (want_stats) {
             int e2 = ensure_partials(c, grid);

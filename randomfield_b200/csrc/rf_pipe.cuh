@@ -227,7 +227,8 @@ constexpr int kBarBytes = 64;   // full[2], done[2] mbarriers
 // ----------------------------------------------------------------------------------------
 struct K3PParams {
   float* buf;              // in: complex [nlines][nz/2]; out: real [nlines][nz] (same bytes)
-  int ntiles;              // nlines / TL
+  int ntiles;              // tiles to process (nlines / TL for the whole slab)
+  int tile0;               // first tile (x-chunked runs)
   const cpx<float>* twH;   // exp(+2 pi i k / (nz/2))
   const cpx<float>* twN;   // exp(+2 pi i k / nz), k < nz/2
   const float* zscale;     // optional per-z factor (nz entries) or nullptr
@@ -263,7 +264,7 @@ __global__ void __launch_bounds__(kThreads, 1) k3p_c2r_lines(const K3PParams p) 
   __syncthreads();
 
   const int first = blockIdx.x, step = gridDim.x;
-  char* gbase = reinterpret_cast<char*>(p.buf);
+  char* gbase = reinterpret_cast<char*>(p.buf) + (size_t)p.tile0 * P::kDenseBytes;
   constexpr size_t kTile = P::kDenseBytes;
 
   if (tid >= kConsumers) {
@@ -410,7 +411,8 @@ __global__ void __launch_bounds__(kThreads, 1) k3p_c2r_lines(const K3PParams p) 
 // ----------------------------------------------------------------------------------------
 struct K2PParams {
   const cpx<float>* tw;    // exp(+2 pi i k / N)
-  int ntiles;              // outer * ztiles
+  int ntiles;              // tiles to process (outer * ztiles for the whole slab)
+  int tile0;               // first tile (x-chunked runs); a multiple of ztiles
   int ztiles;              // ncols / TZ
   int rows_per_src;        // rows of a line held by one source block (N when single GPU)
   int box_rows;            // rows per TMA box = min(256, rows_per_src)
@@ -451,6 +453,7 @@ k2p_strided_fft(const __grid_constant__ CUtensorMap map_in, const __grid_constan
       tma_prefetch_desc(&map_in);
       tma_prefetch_desc(&map_out);
       auto load_tile = [&](int t, int b) {
+        t += p.tile0;
         const int o = t / p.ztiles, z0 = (t % p.ztiles) * P::TZ;
         mbar_expect_tx(&full[b], (uint32_t)P::kDenseBytes);
         for (int r0 = 0; r0 < N; r0 += p.box_rows) {
@@ -464,7 +467,7 @@ k2p_strided_fft(const __grid_constant__ CUtensorMap map_in, const __grid_constan
       for (int t = first; t < p.ntiles; t += step, ++i) {
         const int b = i & 1;
         mbar_wait(&done[b], (i >> 1) & 1);
-        const int o = t / p.ztiles, z0 = (t % p.ztiles) * P::TZ;
+        const int o = (t + p.tile0) / p.ztiles, z0 = ((t + p.tile0) % p.ztiles) * P::TZ;
         for (int r0 = 0; r0 < N; r0 += P::kBoxRows)
           tma_store_3d(&map_out, dense0 + b * kDenseElems + r0 * P::TZ, 2 * z0, r0, o);
         bulk_commit();

@@ -97,3 +97,42 @@ class SlabEngine(object):
 
     def local_field(self):
         return self.engine.copy_field()
+
+
+def run_virtual_slabs(nx, ny, nz, spacing, power, seed, world, smoothing=0.0, dtype=np.float32,
+                      potential=False, zscale=None):
+    """All `world` ranks of the slab pipeline driven from ONE process on ONE GPU: each rank's
+    engine generates its y-slab, the all-to-all is done with device copies between the
+    engines' buffers, each rank finishes its x-slab.  Returns (field (nx, ny, nz), mean, std).
+    Used to check that the field is bit-identical for every decomposition."""
+    import torch
+    shape = (nx, ny, nz)
+    k, sig = powertools.sigma_table(powertools.filter_power(power, smoothing), shape, spacing)
+    engines = [_lib.Engine(nx, ny, nz, dtype=dtype, rank=r, world=world) for r in range(world)]
+    itemsize = engines[0].complex_dtype.itemsize
+    xfer = nx * (ny // world) * (nz // 2) * itemsize
+    for e in engines:
+        e.set_power(k, sig, spacing)
+        e.generate_xpass(seed, potential)
+        e.sync()
+    if world > 1:
+        sends = [e.torch_view(_lib.RF_BUF_FIELD, xfer).view(world, -1) for e in engines]
+        recvs = [e.torch_view(_lib.RF_BUF_RECV, xfer).view(world, -1) for e in engines]
+        for d in range(world):
+            for s in range(world):
+                recvs[d][s].copy_(sends[s][d])
+        torch.cuda.synchronize()
+    s1 = s2 = 0.0
+    n = 0
+    parts = []
+    for e in engines:
+        if world > 1:
+            e.finish_yz(zscale, True)
+        else:
+            e.finish_yz(zscale, True)
+        a, b, c = e.stats()
+        s1, s2, n = s1 + a, s2 + b, n + c
+        parts.append(e.copy_field())
+        e.close()
+    mean = s1 / n
+    return np.concatenate(parts, axis=0), mean, float(np.sqrt(max(s2 / n - mean * mean, 0.0)))

@@ -1,0 +1,71 @@
+"""Slab decomposition on the GPU (gate 3 of BASELINE.json north_star): the Philox field must be
+bit-identical at 1, 2, 4 and 8 ranks.  On a one-GPU box the ranks are driven from one process
+(slab.run_virtual_slabs: same kernels, same buffers, device copies for the all-to-all); with
+two or more GPUs the real torch.distributed/NCCL path is run under torchrun as well."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("shape", [(64, 64, 64), (128, 256, 64), (256, 128, 128)])
+def test_field_bit_identical_across_decompositions(shape):
+    from randomfield_b200 import slab
+    power = oracle.load_default_power()
+    ref, mean1, std1 = slab.run_virtual_slabs(*shape, 2.0, power, seed=99, world=1)
+    assert np.isfinite(ref).all() and abs(std1 - ref.std(dtype=np.float64)) < 1e-5 * std1
+    for world in (2, 4, 8):
+        got, mean, std = slab.run_virtual_slabs(*shape, 2.0, power, seed=99, world=world)
+        assert np.array_equal(got, ref), "world=%d" % world
+        assert abs(std - std1) <= 1e-9 * std1
+
+
+def test_slab_field_matches_oracle():
+    """and the decomposed field is the right field: Philox restatement + numpy irfftn."""
+    from randomfield_b200 import slab
+    shape, spacing, seed = (64, 128, 64), 2.0, 7
+    power = oracle.load_default_power()
+    kf, _ = oracle.philox_kfield(shape, spacing, power, seed)
+    truth = np.fft.irfftn(kf, s=shape, axes=(0, 1, 2))
+    got, _, _ = slab.run_virtual_slabs(*shape, spacing, power, seed=seed, world=4)
+    err = np.sqrt(np.mean((got - truth) ** 2)) / truth.std()
+    assert err <= 1e-5
+
+
+def test_potential_and_zscale_across_decompositions():
+    from randomfield_b200 import slab
+    shape = (64, 64, 128)
+    power = oracle.load_default_power()
+    zs = np.linspace(0.5, 1.5, shape[2])
+    ref, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=3, world=1, potential=True, zscale=zs)
+    got, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=3, world=2, potential=True, zscale=zs)
+    assert np.array_equal(got, ref)
+
+
+def _ngpu():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs two GPUs")
+def test_nccl_two_ranks_matches_single(tmp_path):
+    """Real one-process-per-GPU run: rank slabs written to disk, compared with world=1."""
+    script = os.path.join(ROOT, "tests", "multi_worker.py")
+    out = str(tmp_path)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29533", script, out]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    from randomfield_b200 import slab
+    ref, _, std1 = slab.run_virtual_slabs(128, 128, 64, 2.0, oracle.load_default_power(), seed=42, world=1)
+    got = np.concatenate([np.load(os.path.join(out, "rank%d.npy" % r)) for r in range(2)], axis=0)
+    assert np.array_equal(got, ref)
+    std = float(open(os.path.join(out, "std.txt")).read())
+    assert abs(std - std1) <= 1e-9 * std1

@@ -1,0 +1,133 @@
+"""CPU tests of the host-side mirror of the reference interface (table-sized logic that stays
+in Python) and of the slab-decomposition bookkeeping, incl. a world_size-2 gloo exchange."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from randomfield_b200 import powertools, slab, transform
+
+
+# ---- reference tests/test_powertools.py:53-96 re-hosted ---------------------------------------
+def _power(n=10):
+    p = np.empty(n, dtype=[('k', float), ('Pk', float)])
+    p['k'] = np.linspace(0.01, 10., n)
+    p['Pk'] = 1.0
+    return p
+
+
+def test_validate_power_accepts_default():
+    assert len(powertools.validate_power(powertools.load_default_power())) == 500
+
+
+@pytest.mark.parametrize("mutate", [
+    lambda p: p.tolist(),
+    lambda p: p[['k']],
+    lambda p: _set(p, 'k', 3, np.nan),
+    lambda p: _set(p, 'Pk', 3, np.inf),
+    lambda p: _set(p, 'k', 3, p['k'][2]),
+    lambda p: _set(p, 'k', 0, 0.0),
+    lambda p: _set(p, 'Pk', 4, -1.0),
+])
+def test_validate_power_rejects(mutate):
+    with pytest.raises(ValueError):
+        powertools.validate_power(mutate(_power()))
+
+
+def _set(p, field, i, v):
+    p = p.copy()
+    p[field][i] = v
+    return p
+
+
+def test_filter_power_matches_oracle_and_rejects_negative():
+    p = powertools.load_default_power()
+    a, b = powertools.filter_power(p, 3.0), oracle.filter_power(oracle.load_default_power(), 3.0)
+    assert np.array_equal(a['Pk'], b['Pk'])
+    assert np.array_equal(powertools.filter_power(p, 0.0)['Pk'], p['Pk'])
+    with pytest.raises(ValueError):
+        powertools.filter_power(p, -1.0)
+
+
+def test_k_bounds_and_sigma_table():
+    data = np.empty((4, 6, 5), dtype=np.complex64)
+    assert powertools.get_k_bounds(data, 2.5) == pytest.approx(oracle.get_k_bounds((4, 6, 8), 2.5))
+    k, sig = powertools.sigma_table(powertools.load_default_power(), (64, 64, 64), 2.0)
+    lk, osig = oracle.sigma_table(oracle.load_default_power(), (64, 64, 64), 2.0)
+    assert np.array_equal(sig, osig) and np.allclose(np.log10(k), lk)
+    with pytest.raises(ValueError):     # table does not cover the grid's k range: powertools.py:147-150
+        powertools.sigma_table(_power(), (64, 64, 64), 0.01)
+
+
+def test_transform_type_helpers():
+    assert transform.scalar_type(np.complex64) == np.float32
+    assert transform.complex_type(np.float64) == np.complex128
+    with pytest.raises(ValueError):
+        transform.scalar_type(np.float32)
+    with pytest.raises(ValueError):
+        transform.expanded_shape(np.empty((3, 4, 4)))
+    with pytest.raises(ValueError):
+        transform.expanded_shape(np.empty((4, 4, 4)), packed=True)
+    assert transform.expanded_shape(np.empty((4, 6, 5)), packed=True) == (4, 6, 8)
+
+
+# ---- slab decomposition ---------------------------------------------------------------------------
+def test_slab_ranges():
+    assert slab.slab_ranges(64, 4, 1) == (16, 32)
+    with pytest.raises(ValueError):
+        slab.slab_ranges(10, 4, 0)
+    assert slab.block_elems(64, 32, 16, 4) == 16 * 8 * 8
+
+
+def _slab_reference(shape, world):
+    """numpy emulation of the slab pipeline in the internal packed-Nyquist layout: returns the
+    per-rank x-slabs and the single-rank result they must equal bit for bit."""
+    nx, ny, nz = shape
+    rng = np.random.RandomState(4)
+    kf = (rng.normal(size=(nx, ny, nz // 2)) + 1j * rng.normal(size=(nx, ny, nz // 2))).astype(np.complex64)
+    full = np.fft.ifft(np.fft.ifft(kf, axis=0), axis=1)
+    nyl, nxl = ny // world, nx // world
+    sends = [np.ascontiguousarray(np.fft.ifft(kf[:, r * nyl:(r + 1) * nyl], axis=0)) for r in range(world)]
+    return kf, full, sends, nxl, nyl
+
+
+def test_recv_layout_single_process():
+    shape, world = (8, 12, 8), 4
+    _, full, sends, nxl, nyl = _slab_reference(shape, world)
+    nzc = shape[2] // 2
+    for d in range(world):
+        recv = np.stack([s.reshape(world, nxl, nyl, nzc)[d] for s in sends])
+        rows = slab.recv_to_rows(recv, *shape, world)
+        assert np.array_equal(np.fft.ifft(rows, axis=1), full[d * nxl:(d + 1) * nxl])
+
+
+def _gloo_worker(rank, world, port, shape, out):
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        _, full, sends, nxl, nyl = _slab_reference(shape, world)
+        send = torch.from_numpy(sends[rank].view(np.float32).copy())
+        recv = torch.empty_like(send)
+        slab.all_to_all(send, recv)
+        rows = slab.recv_to_rows(recv.numpy().view(np.complex64).reshape(-1), *shape, world)
+        ok = np.array_equal(np.fft.ifft(rows, axis=1), full[rank * nxl:(rank + 1) * nxl])
+        # global statistics: the two-double all-reduce of SlabEngine.global_stats
+        t = torch.tensor([float(rank + 1), float((rank + 1) ** 2), 1.0], dtype=torch.float64)
+        dist.all_reduce(t)
+        ok = ok and t.tolist() == [3.0, 5.0, 2.0]
+        out[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_all_to_all_gloo_world2():
+    import torch.multiprocessing as mp
+    world, port = 2, 29541 + os.getpid() % 200
+    with mp.Manager() as mgr:
+        out = mgr.dict()
+        mp.spawn(_gloo_worker, args=(world, port, (8, 12, 8), out), nprocs=world, join=True)
+        assert dict(out) == {0: True, 1: True}
