@@ -36,6 +36,7 @@ WEAK_GRIDS = {1: (1024, 1024, 1024), 2: (2048, 2048, 512), 4: (2048, 2048, 1024)
 BYTES_PER_CELL = 20.0          # f32: write 4 + (read 4 + write 4) x 2   
 PASS_BYTES_PER_CELL = (4.0, 8.0, 8.0)
 PASS_NAMES = ("k1_generate_xfft", "k2_strided_fft", "k3_c2r_lines")
+PIPE_NAMES = ("k1p_generate_xfft", "k2p_strided_fft", "k3p_c2r_lines")
 
 
 def measured_peaks():
@@ -205,6 +206,7 @@ def run_ours(args):
     pass_ms /= nprobe
     clocks = sampler.stop() if rank == 0 else None
     mean, std = eng.global_stats()
+    pipelined = eng.engine.is_pipelined
     if world > 1:
         t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -227,7 +229,16 @@ def run_ours(args):
 
     peak, peak_src = measured_peaks()
     local_cells = cells / world
+    names = PIPE_NAMES if pipelined else PASS_NAMES
     dom = int(np.argmax(pass_ms))
+    traffic = None
+    try:   # DRAM bytes per launch from the committed ncu --set full capture of the same workload
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            tj = json.load(f)
+        if tj.get("grid") == list(grid) and world == 1:
+            traffic = tj["dram_bytes_per_launch"].get(names[dom])
+    except Exception:
+        pass
     dom_bytes = PASS_BYTES_PER_CELL[dom] * local_cells
     achieved = dom_bytes / (pass_ms[dom] * 1e-3) / 1e9
     step_achieved = BYTES_PER_CELL * local_cells / (ms_step * 1e-3) / 1e9
@@ -239,14 +250,16 @@ def run_ours(args):
                    "l2": "working set %.1f GB per GPU >> 126 MB L2, no flush needed" % (4 * local_cells / 1e9),
                    "parallelism": "y-slab k-space -> all-to-all -> x-slab real space" if world > 1 else "single GPU",
                    "field_std": std, "field_mean": mean},
-        "roofline": {"bound": "hbm", "kernel": PASS_NAMES[dom], "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "roofline": {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": dom_bytes},
         "roofline_step": {"bytes_per_cell": BYTES_PER_CELL, "achieved": step_achieved, "peak": peak,
                           "unit": "GB/s", "frac": step_achieved / peak,
                           "frac_of_8TBs": step_achieved / 8000.0},
-        "kernels_ms": dict(zip(PASS_NAMES, [float(v) for v in pass_ms])),
+        "kernels_ms": dict(zip(names, [float(v) for v in pass_ms])),
+        "kernels_gbs": dict(zip(names, [float(b * local_cells / (t * 1e-3) / 1e9)
+                                        for b, t in zip(PASS_BYTES_PER_CELL, pass_ms)])),
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
     }
     if world > 1:

@@ -133,6 +133,9 @@ void* rf_device_ptr(rf_ctx* ctx, int which);
 long long rf_buffer_bytes(rf_ctx* ctx, int which);
 /* 1 if the (nx, ny, nz, dtype) grid runs on the tile kernels, 0 if on the generic path */
 int rf_is_fast(rf_ctx* ctx);
+/* 1 if the hot path runs on the persistent TMA-pipelined kernels (k1p/k2p/k3p: float32, axes of
+ * 64..1024 points, 2048 for z), 0 if on the rf_fast.cuh tile kernels or the generic path */
+int rf_is_pipelined(rf_ctx* ctx);
 /* number of kernels launched by this context so far */
 long long rf_launch_count(rf_ctx* ctx);
 

@@ -50,6 +50,7 @@ SIGNATURES = {
     "rf_device_ptr": (_P, [_P, _c.c_int]),
     "rf_buffer_bytes": (_c.c_longlong, [_P, _c.c_int]),
     "rf_is_fast": (_c.c_int, [_P]),
+    "rf_is_pipelined": (_c.c_int, [_P]),
     "rf_launch_count": (_c.c_longlong, [_P]),
 }
 
@@ -231,6 +232,10 @@ class Engine:
     @property
     def is_fast(self):
         return bool(lib().rf_is_fast(self._ctx))
+
+    @property
+    def is_pipelined(self):
+        return bool(lib().rf_is_pipelined(self._ctx))
 
     @property
     def launch_count(self):

@@ -200,6 +200,9 @@ extern "C" int rf_get_timing(rf_ctx* c, double* a, double* b, double* d) {
   return RF_OK;
 }
 extern "C" int rf_is_fast(rf_ctx* c) { return c && c->fast ? 1 : 0; }
+extern "C" int rf_is_pipelined(rf_ctx* c) {
+  return c && c->pipe && c->nx <= 1024 && c->ny <= 1024 && c->nz <= 2048 ? 1 : 0;
+}
 extern "C" long long rf_launch_count(rf_ctx* c) { return c ? c->launches : 0; }
 extern "C" long long rf_field_elems(rf_ctx* c) {
   return c ? (long long)c->nxl * c->ny * c->nz : 0;
