@@ -61,7 +61,7 @@ class ClockSampler(object):
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "50"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -217,6 +217,25 @@ def run_ours(args):
     ms_step = ms_total / args.steps
     value = cells / (ms_step * 1e-3) / 1e6
 
+    # BASELINE config 3 add-ons (device-timed, this rank's slab): lognormal density pass and the
+    # Newtonian potential (regenerated with the 1/k^2 factor, light-cone factor in the epilogue)
+    extras = None
+    if world == 1:
+        nzl = grid[2]
+        growth = 1.0 / (1.0 + np.linspace(0.0, 1.0, nzl))
+        rho = np.full(nzl, 1e-29)
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        with torch.cuda.stream(stream):
+            eng.engine.generate_delta(77, False, None, True)
+            e0.record(stream)
+            eng.engine.density(True, std, growth, rho)
+            e1.record(stream)
+            eng.engine.generate_delta(77, True, growth * -4.8e-36, False)
+            e2.record(stream)
+        torch.cuda.synchronize()
+        extras = {"lognormal_density_ms": e0.elapsed_time(e1), "newtonian_potential_ms": e1.elapsed_time(e2),
+                  "bytes_per_cell": {"lognormal_density": 8, "newtonian_potential": 20}}
+
     # ---- end to end through the public API (N=1: Generator; N>1: slab + host copy) ------
     e2e = None
     if (rank == 0 or world > 1) and not args.no_e2e:
@@ -260,6 +279,7 @@ def run_ours(args):
         "kernels_ms": dict(zip(names, [float(v) for v in pass_ms])),
         "kernels_gbs": dict(zip(names, [float(b * local_cells / (t * 1e-3) / 1e9)
                                         for b, t in zip(PASS_BYTES_PER_CELL, pass_ms)])),
+        "config3_addons": extras,
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
     }
     if world > 1:
@@ -323,7 +343,7 @@ def run_e2e(args, grid, world, rank, eng, barrier):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--grid", default=None, help="nx,ny,nz override")

@@ -40,6 +40,8 @@ struct rf_ctx {
   int nxl = 0, nyl = 0;     // local slab extents
   bool fast = false;
   bool pipe = false;        // TMA-pipelined kernels (f32, env RF_PIPE != 0)
+  bool fuse = false;        // fused y+z kernel k23p (env RF_FUSE != 0)
+  unsigned int* sched = nullptr;   // [1 + nxl] ticket + per-plane counters of k23p
   int num_sms = 148;
   size_t esize = 4;         // sizeof(T)
   cudaStream_t own_stream = nullptr, stream = nullptr;
@@ -119,6 +121,9 @@ extern "C" int rf_create(int nx, int ny, int nz, int dtype, int rank, int world,
     cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, dev);
     const char* env = getenv("RF_PIPE");
     c->pipe = c->fast && dtype == RF_F32 && !(env && env[0] == '0');
+    const char* envf = getenv("RF_FUSE");
+    // opt-in: measured slower than k2p + k3p on B200, kept for the L2-reuse work
+    c->fuse = c->pipe && ny <= 1024 && nz <= 2048 && envf && envf[0] == '1';
   }
   RF_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
   c->stream = c->own_stream;
@@ -152,7 +157,7 @@ extern "C" int rf_destroy(rf_ctx* c) {
   if (!c) return RF_OK;
   cudaStreamSynchronize(c->stream);
   void* ptrs[] = {c->field, c->recv, c->partials, c->stats_dev, c->tw_x, c->tw_y, c->tw_z,
-                  c->tw_zh, c->knots, c->cells, c->hinge, c->plane, c->noise, c->zs_dev, c->da_dev, c->db_dev};
+                  c->tw_zh, c->knots, c->cells, c->hinge, c->plane, c->sched, c->noise, c->zs_dev, c->da_dev, c->db_dev};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -647,7 +652,7 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
       p2.rows_per_src = c->ny;
     }
     int e = 0;
-    bool done2 = false;
+    bool done2 = false, fused_done = false;
     if constexpr (std::is_same<T, float>::value) {
       if (c->pipe && c->ny <= 1024) {
         pipe::K2PParams q;
@@ -673,9 +678,45 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
           if (e2) return e2;
           q.tile0 = 0;
           int grid = std::min(q.ntiles, c->num_sms);
-          mark(c, 2);
-          e = PipeLaunch<NN>::k2p(min, mout, q, grid, c->stream);
-          mark(c, 3);
+          const int t3_per_plane = (int)((long long)c->ny * (c->nz / 2) * 8 / pipe::kTileBytes);
+          if (c->fuse && t3_per_plane >= 1) {
+            // y and z passes in one persistent kernel (z pass reads the y-pass output from L2)
+            pipe::K23Params f;
+            f.k2 = q;
+            f.k3.buf = (float*)c->field;
+            f.k3.twH = (const cpx<float>*)c->tw_zh;
+            f.k3.twN = (const cpx<float>*)c->tw_z;
+            f.k3.zscale = zs;
+            f.k3.partials = nullptr;
+            f.k3.ntiles = 0; f.k3.tile0 = 0;
+            f.nplanes = c->nxl;
+            f.t2 = q.ztiles;
+            f.t3 = t3_per_plane;
+            // far enough apart that a plane's y pass has normally drained when its z pass starts
+            f.lag = std::min(c->nxl, std::max(1, (3 * c->num_sms) / (f.t2 + f.t3) + 1));
+            if (const char* el = getenv("RF_LAG")) f.lag = std::min(c->nxl, std::max(1, atoi(el)));
+            if (!c->sched) RF_CUDA(cudaMalloc((void**)&c->sched, sizeof(unsigned int) * (1 + c->nxl)));
+            RF_CUDA(cudaMemsetAsync(c->sched, 0, sizeof(unsigned int) * (1 + c->nxl), c->stream));
+            f.ticket = c->sched;
+            f.plane_done = c->sched + 1;
+            const int total = c->nxl * (f.t2 + f.t3);
+            grid = std::min(total, c->num_sms);
+            if (want_stats) {
+              int e2 = ensure_partials(c, grid);
+              if (e2) return e2;
+              f.k3.partials = c->partials;
+            }
+            mark(c, 2);
+            e = PipeLaunch<NN>::k23p(c->nz, min, mout, f, grid, c->stream);
+            mark(c, 3);
+            mark(c, 4);
+            mark(c, 5);
+            fused_done = true;
+          } else {
+            mark(c, 2);
+            e = PipeLaunch<NN>::k2p(min, mout, q, grid, c->stream);
+            mark(c, 3);
+          }
         });
         c->launches++;
         RF_CUDA(e);
@@ -692,9 +733,9 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
       c->launches++;
       RF_CUDA(e);
     }
-    bool done3 = false;
+    bool done3 = fused_done;
     if constexpr (std::is_same<T, float>::value) {
-      if (c->pipe && c->nz <= 2048) {
+      if (!fused_done && c->pipe && c->nz <= 2048) {
         pipe::K3PParams q;
         q.buf = (float*)c->field;
         q.twH = (const cpx<float>*)c->tw_zh;

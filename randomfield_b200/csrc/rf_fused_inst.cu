@@ -1,0 +1,37 @@
+// rf_fused_inst.cu -- instantiations of the fused y+z kernel k23p for one NY (all NZ):
+//   -DRF_PIPE_N=<64..1024>
+#include "rf_launch.h"
+
+#ifndef RF_PIPE_N
+#error "define RF_PIPE_N"
+#endif
+
+namespace rf {
+
+constexpr int NY = RF_PIPE_N;
+
+template <int NZ>
+static int launch23(const CUtensorMap& in, const CUtensorMap& out, const pipe::K23Params& p, int grid,
+                    cudaStream_t s) {
+  constexpr int smem = pipe::k23p_smem_bytes<NY, NZ>();
+  int e = (int)cudaFuncSetAttribute(pipe::k23p_fused_yz<NY, NZ>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e) return e;
+  pipe::k23p_fused_yz<NY, NZ><<<grid, pipe::kThreads, smem, s>>>(in, out, p);
+  return (int)cudaGetLastError();
+}
+
+template <>
+int PipeLaunch<NY>::k23p(int nz, const CUtensorMap& in, const CUtensorMap& out, const pipe::K23Params& p,
+                         int grid, cudaStream_t s) {
+  switch (nz) {
+    case 64: return launch23<64>(in, out, p, grid, s);
+    case 128: return launch23<128>(in, out, p, grid, s);
+    case 256: return launch23<256>(in, out, p, grid, s);
+    case 512: return launch23<512>(in, out, p, grid, s);
+    case 1024: return launch23<1024>(in, out, p, grid, s);
+    case 2048: return launch23<2048>(in, out, p, grid, s);
+  }
+  return (int)cudaErrorInvalidValue;
+}
+
+}  // namespace rf

@@ -25,6 +25,9 @@ struct PipeLaunch {
   static int k2p(const CUtensorMap& in, const CUtensorMap& out, const pipe::K2PParams& p, int grid,
                  cudaStream_t s);
   static int k1p(bool injected, bool potential, const CUtensorMap& out, const pipe::K1PParams& p, int grid, cudaStream_t s);
+  // fused y + z pass (this N = ny); nz in 64..2048
+  static int k23p(int nz, const CUtensorMap& in, const CUtensorMap& out, const pipe::K23Params& p, int grid,
+                  cudaStream_t s);
   static int tile_cols();   // TZ
   static int box_rows();    // rows per TMA box of the store map
 };

@@ -220,7 +220,110 @@ __device__ __forceinline__ void load_step_twiddles(cpx<float> (&twr)[R1], const 
   });
 }
 
+// same from a shared-memory copy of the table
+template <int R1>
+__device__ __forceinline__ void load_step_twiddles_smem(cpx<float> (&twr)[R1], const cpx<float>* tws, int j) {
+  sfor<0, R1>([&](auto ki) {
+    constexpr int k1 = decltype(ki)::value;
+    twr[k1] = ld_cpx(tws + j * k1);
+  });
+}
+
 constexpr int kBarBytes = 64;   // full[2], done[2] mbarriers
+
+// FFT-warp work on one k3 tile: Hermitian unpack, step A, step B (+ statistics, z scale).
+// D: dense tile [TL][H]; twr: step-A twiddles of this thread; twu: its unpack twiddle(s).
+template <int NZ>
+struct K3Consts {
+  using P = LPlan<NZ>;
+  static constexpr int H = P::H;
+  static constexpr int kPairsPerThread = (H / 2 + kConsumers - 1) / kConsumers;   // per line
+};
+template <int NZ>
+__device__ __forceinline__ void k3_load_twiddles(cpx<float> (&twr)[LPlan<NZ>::R1],
+                                                 cpx<float> (&twu)[K3Consts<NZ>::kPairsPerThread],
+                                                 const cpx<float>* twH, const cpx<float>* twN, int tid) {
+  constexpr int H = LPlan<NZ>::H;
+  sfor<0, K3Consts<NZ>::kPairsPerThread>([&](auto qi) {
+    constexpr int q = decltype(qi)::value;
+    twu[q] = ldg_cpx(twN + (tid + q * kConsumers) % (H / 2));
+  });
+  load_step_twiddles<LPlan<NZ>::R1>(twr, twH, tid % LPlan<NZ>::M);
+}
+template <int NZ>
+__device__ __forceinline__ void k3_tile_body(cpx<float>* __restrict__ D, cpx<float>* __restrict__ work, int tid,
+                                             const cpx<float> (&twr)[LPlan<NZ>::R1],
+                                             const cpx<float> (&twu)[K3Consts<NZ>::kPairsPerThread],
+                                             const float* zs, float& a1, float& a2) {
+  using P = LPlan<NZ>;
+  constexpr int H = P::H;
+  constexpr int kPairsPerThread = K3Consts<NZ>::kPairsPerThread;
+  using L = LayoutLinesPad<P::WP, P::M>;
+  static_assert(kConsumers % (H / 2) == 0 || (H / 2) % kConsumers == 0, "unpack mapping");
+    // Hermitian unpack in place: Z[k] = E[k] + i*O[k] for the pair (k, H-k)
+    if constexpr (H / 2 >= kConsumers) {
+      // thread owns pairs k = tid + q*kConsumers of every line
+#pragma unroll 2
+      for (int l = 0; l < P::TL; ++l) {
+        cpx<float>* Lp = D + l * H;
+        sfor<0, kPairsPerThread>([&](auto qi) {
+          constexpr int q = decltype(qi)::value;
+          const int k = tid + q * kConsumers;
+          if (q == 0 && k == 0) {
+            cpx<float> a = Lp[0], m = Lp[H / 2];
+            Lp[0] = {a.x + a.y, a.x - a.y};          // X[0], X[H] are real
+            Lp[H / 2] = {2.f * m.x, -2.f * m.y};
+          } else {
+            cpx<float> a = Lp[k], c = Lp[H - k];
+            cpx<float> e = {a.x + c.x, a.y - c.y};   // X[k] + conj(X[H-k])
+            cpx<float> d = {a.x - c.x, a.y + c.y};   // X[k] - conj(X[H-k])
+            cpx<float> o = cmul(d, twu[q]);          // * exp(+2 pi i k / NZ)
+            Lp[k] = {e.x - o.y, e.y + o.x};
+            Lp[H - k] = {e.x + o.y, o.x - e.y};
+          }
+        });
+      }
+    } else {
+      // several lines per sweep: thread owns pair k = tid % (H/2) of lines tid/(H/2) + ...
+      constexpr int kLinesPerSweep = kConsumers / (H / 2);
+      const int k = tid % (H / 2);
+      for (int l = tid / (H / 2); l < P::TL; l += kLinesPerSweep) {
+        cpx<float>* Lp = D + l * H;
+        if (k == 0) {
+          cpx<float> a = Lp[0], m = Lp[H / 2];
+          Lp[0] = {a.x + a.y, a.x - a.y};
+          Lp[H / 2] = {2.f * m.x, -2.f * m.y};
+        } else {
+          cpx<float> a = Lp[k], c = Lp[H - k];
+          cpx<float> e = {a.x + c.x, a.y - c.y};
+          cpx<float> d = {a.x - c.x, a.y + c.y};
+          cpx<float> o = cmul(d, twu[0]);
+          Lp[k] = {e.x - o.y, e.y + o.x};
+          Lp[H - k] = {e.x + o.y, o.x - e.y};
+        }
+      }
+    }
+    ConsumerSync()();
+
+    step_a<H, P::R1, L>(work, tid, P::TL, twr, [&](cpx<float>(&v)[P::R1], int j, int l) {
+      const cpx<float>* Lp = D + l * H + j;
+      sfor<0, P::R1>([&](auto mi) {
+        constexpr int m = decltype(mi)::value;
+        v[m] = ld_cpx(Lp + P::M * m);
+      });
+    });
+    ConsumerSync()();
+    step_b<H, P::R1, L>(work, tid, P::TL, [&](int k, int l, cpx<float> x) {
+      a1 += x.x + x.y;
+      a2 = fmaf(x.x, x.x, fmaf(x.y, x.y, a2));
+      if (zs) {
+        float2 z = __ldg(reinterpret_cast<const float2*>(zs) + k);
+        x.x *= z.x;
+        x.y *= z.y;
+      }
+      st_cpx(D + l * H + k, x);
+    });
+}
 
 // ----------------------------------------------------------------------------------------
 // k3p: c2r along the contiguous axis, packed-Nyquist input, in place (see k3_c2r_lines)
@@ -296,86 +399,17 @@ __global__ void __launch_bounds__(kThreads, 1) k3p_c2r_lines(const K3PParams p) 
   // ===== FFT warps =====
   double s1 = 0.0, s2 = 0.0;
   const float* zs = p.zscale;
-  // per-thread constants: the unpack pair index k, its twiddle, and the step-A twiddles
-  static_assert(kConsumers % (H / 2) == 0 || (H / 2) % kConsumers == 0, "unpack mapping");
-  constexpr int kPairsPerThread = (H / 2 + kConsumers - 1) / kConsumers;   // per line
-  cpx<float> twu[kPairsPerThread];
-  sfor<0, kPairsPerThread>([&](auto qi) {
-    constexpr int q = decltype(qi)::value;
-    twu[q] = ldg_cpx(p.twN + (tid + q * kConsumers) % (H / 2));
-  });
   cpx<float> twr[P::R1];
-  load_step_twiddles<P::R1>(twr, p.twH, tid % P::M);
+  cpx<float> twu[K3Consts<NZ>::kPairsPerThread];
+  k3_load_twiddles<NZ>(twr, twu, p.twH, p.twN, tid);
   int i = 0;
   for (int t = first; t < p.ntiles; t += step, ++i) {
     const int b = i & 1;
     cpx<float>* const D = dense0 + b * kDenseElems;
     mbar_wait(&full[b], (i >> 1) & 1);
 
-    // Hermitian unpack in place: Z[k] = E[k] + i*O[k] for the pair (k, H-k)
-    if constexpr (H / 2 >= kConsumers) {
-      // thread owns pairs k = tid + q*kConsumers of every line
-#pragma unroll 2
-      for (int l = 0; l < P::TL; ++l) {
-        cpx<float>* Lp = D + l * H;
-        sfor<0, kPairsPerThread>([&](auto qi) {
-          constexpr int q = decltype(qi)::value;
-          const int k = tid + q * kConsumers;
-          if (q == 0 && k == 0) {
-            cpx<float> a = Lp[0], m = Lp[H / 2];
-            Lp[0] = {a.x + a.y, a.x - a.y};          // X[0], X[H] are real
-            Lp[H / 2] = {2.f * m.x, -2.f * m.y};
-          } else {
-            cpx<float> a = Lp[k], c = Lp[H - k];
-            cpx<float> e = {a.x + c.x, a.y - c.y};   // X[k] + conj(X[H-k])
-            cpx<float> d = {a.x - c.x, a.y + c.y};   // X[k] - conj(X[H-k])
-            cpx<float> o = cmul(d, twu[q]);          // * exp(+2 pi i k / NZ)
-            Lp[k] = {e.x - o.y, e.y + o.x};
-            Lp[H - k] = {e.x + o.y, o.x - e.y};
-          }
-        });
-      }
-    } else {
-      // several lines per sweep: thread owns pair k = tid % (H/2) of lines tid/(H/2) + ...
-      constexpr int kLinesPerSweep = kConsumers / (H / 2);
-      const int k = tid % (H / 2);
-      for (int l = tid / (H / 2); l < P::TL; l += kLinesPerSweep) {
-        cpx<float>* Lp = D + l * H;
-        if (k == 0) {
-          cpx<float> a = Lp[0], m = Lp[H / 2];
-          Lp[0] = {a.x + a.y, a.x - a.y};
-          Lp[H / 2] = {2.f * m.x, -2.f * m.y};
-        } else {
-          cpx<float> a = Lp[k], c = Lp[H - k];
-          cpx<float> e = {a.x + c.x, a.y - c.y};
-          cpx<float> d = {a.x - c.x, a.y + c.y};
-          cpx<float> o = cmul(d, twu[0]);
-          Lp[k] = {e.x - o.y, e.y + o.x};
-          Lp[H - k] = {e.x + o.y, o.x - e.y};
-        }
-      }
-    }
-    ConsumerSync()();
-
     float a1 = 0.f, a2 = 0.f;
-    step_a<H, P::R1, L>(work, tid, P::TL, twr, [&](cpx<float>(&v)[P::R1], int j, int l) {
-      const cpx<float>* Lp = D + l * H + j;
-      sfor<0, P::R1>([&](auto mi) {
-        constexpr int m = decltype(mi)::value;
-        v[m] = ld_cpx(Lp + P::M * m);
-      });
-    });
-    ConsumerSync()();
-    step_b<H, P::R1, L>(work, tid, P::TL, [&](int k, int l, cpx<float> x) {
-      a1 += x.x + x.y;
-      a2 = fmaf(x.x, x.x, fmaf(x.y, x.y, a2));
-      if (zs) {
-        float2 z = __ldg(reinterpret_cast<const float2*>(zs) + k);
-        x.x *= z.x;
-        x.y *= z.y;
-      }
-      st_cpx(D + l * H + k, x);
-    });
+    k3_tile_body<NZ>(D, work, tid, twr, twu, zs, a1, a2);
     s1 += (double)a1;
     s2 += (double)a2;
     fence_proxy_async();
@@ -399,6 +433,23 @@ __global__ void __launch_bounds__(kThreads, 1) k3p_c2r_lines(const K3PParams p) 
       p.partials[2 * (size_t)blockIdx.x + 1] = t2;
     }
   }
+}
+
+// FFT-warp work on one k2 tile (dense [N][TZ], in place through the padded work buffer)
+template <int N>
+__device__ __forceinline__ void k2_tile_body(cpx<float>* __restrict__ D, cpx<float>* __restrict__ work, int tid,
+                                             const cpx<float> (&twr)[SPlan<N>::R1]) {
+  using P = SPlan<N>;
+  using L = LayoutStridedPad<P::TZ, P::M>;
+  step_a<N, P::R1, L>(work, tid, P::TZ, twr, [&](cpx<float>(&v)[P::R1], int jj, int cc) {
+    const cpx<float>* Dp = D + jj * P::TZ + cc;
+    sfor<0, P::R1>([&](auto mi) {
+      constexpr int m = decltype(mi)::value;
+      v[m] = ld_cpx(Dp + P::M * m * P::TZ);
+    });
+  });
+  ConsumerSync()();
+  step_b<N, P::R1, L>(work, tid, P::TZ, [&](int k, int cc, cpx<float> x) { st_cpx(D + k * P::TZ + cc, x); });
 }
 
 // ----------------------------------------------------------------------------------------
@@ -490,15 +541,7 @@ k2p_strided_fft(const __grid_constant__ CUtensorMap map_in, const __grid_constan
     const int b = i & 1;
     cpx<float>* const D = dense0 + b * kDenseElems;
     mbar_wait(&full[b], (i >> 1) & 1);
-    step_a<N, P::R1, L>(work, tid, P::TZ, twr, [&](cpx<float>(&v)[P::R1], int jj, int cc) {
-      const cpx<float>* Dp = D + jj * P::TZ + cc;
-      sfor<0, P::R1>([&](auto mi) {
-        constexpr int m = decltype(mi)::value;
-        v[m] = ld_cpx(Dp + P::M * m * P::TZ);
-      });
-    });
-    ConsumerSync()();
-    step_b<N, P::R1, L>(work, tid, P::TZ, [&](int k, int cc, cpx<float> x) { st_cpx(D + k * P::TZ + cc, x); });
+    k2_tile_body<N>(D, work, tid, twr);
     fence_proxy_async();
     mbar_arrive(&done[b]);
     // the next tile's step A overwrites the work buffer: everyone must be out of step B
@@ -611,6 +654,267 @@ k1p_generate_xfft(const __grid_constant__ CUtensorMap map_out, const K1PParams p
   }
   if (tid == 0) bulk_wait0();
   (void)c;
+}
+
+// ----------------------------------------------------------------------------------------
+// k23p: the y pass and the z (c2r) pass in ONE persistent kernel, so that the y-pass output of
+// an x-plane is still in L2 when the z pass reads it (the plane's tiles are visited a few
+// planes later, and the 126 MB L2 is write-back): DRAM sees 8 B/cell for both passes instead
+// of 16.  Tiles are handed out by a global ticket in a fixed order
+//     K2(plane 0) ... K2(plane lag-1), K2(plane lag), K3(plane 0), K2(plane lag+1), K3(plane 1), ...
+// (CTA c owns tickets c, c + grid, c + 2*grid, ...).  A K3 tile waits until the ztiles K2 tiles of
+// its plane have been stored (plane_done counter).  It only depends on smaller tickets and every
+// CTA works through its tickets in increasing order, blocking only when all of its own earlier
+// tiles are stored and signalled, so the smallest unfinished ticket can always proceed.
+// ----------------------------------------------------------------------------------------
+struct K23Params {
+  K2PParams k2;               // ntiles / tile0 unused
+  K3PParams k3;               // ntiles / tile0 unused
+  int nplanes;                // local x planes
+  int t2, t3;                 // K2 / K3 tiles per plane
+  int lag;                    // planes between the y pass and the z pass (<= nplanes)
+  unsigned int* ticket;       // zeroed before launch
+  unsigned int* plane_done;   // [nplanes] zeroed before launch
+};
+
+enum { kTileK2 = 0, kTileK3 = 1, kTileEnd = 2 };
+
+__device__ __forceinline__ void k23_decode(const K23Params& p, unsigned int ticket, int& type, int& plane,
+                                           int& idx) {
+  const unsigned int head = (unsigned)p.lag * p.t2, per = (unsigned)(p.t2 + p.t3);
+  const unsigned int mid = (unsigned)(p.nplanes - p.lag) * per;
+  const unsigned int total = (unsigned)p.nplanes * per;
+  if (ticket >= total) { type = kTileEnd; plane = idx = 0; return; }
+  if (ticket < head) { type = kTileK2; plane = ticket / p.t2; idx = ticket % p.t2; return; }
+  unsigned int u = ticket - head;
+  if (u < mid) {
+    const int s = p.lag + u / per, r = u % per;
+    if (r < p.t2) { type = kTileK2; plane = s; idx = r; }
+    else { type = kTileK3; plane = s - p.lag; idx = r - p.t2; }
+    return;
+  }
+  u -= mid;
+  type = kTileK3; plane = p.nplanes - p.lag + u / p.t3; idx = u % p.t3;
+}
+
+template <int NY, int NZ>
+constexpr int k23p_smem_bytes() {
+  // dense ring, work buffer, barriers + tile descriptors, twiddle tables (NY + 2*(NZ/2) entries)
+  return 2 * kTileBytes + (SPlan<NY>::kWorkBytes > LPlan<NZ>::kWorkBytes ? SPlan<NY>::kWorkBytes
+                                                                          : LPlan<NZ>::kWorkBytes) + 2 * kBarBytes +
+         (NY + NZ) * 8;
+}
+
+template <int NY, int NZ>
+__global__ void __launch_bounds__(kThreads, 1)
+k23p_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_out,
+              const K23Params p) {
+  using P2 = SPlan<NY>;
+  using P3 = LPlan<NZ>;
+  static_assert(P2::kDenseBytes <= kTileBytes && P3::kDenseBytes <= kTileBytes, "tile size");
+  constexpr int kWork = SPlan<NY>::kWorkBytes > LPlan<NZ>::kWorkBytes ? SPlan<NY>::kWorkBytes : LPlan<NZ>::kWorkBytes;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  cpx<float>* const dense0 = reinterpret_cast<cpx<float>*>(smem_raw);
+  constexpr int kDenseElems = kTileBytes / 8;
+  cpx<float>* const work = reinterpret_cast<cpx<float>*>(smem_raw + 2 * kTileBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + 2 * kTileBytes + kWork);
+  uint64_t* full = bars;
+  uint64_t* done = bars + 2;
+  volatile int* desc = reinterpret_cast<volatile int*>(bars + 8);   // [2][4]: type, plane, idx
+  // The acquire loads / release reductions of the copy warp invalidate L1 (CCTL.IVALL), so the
+  // per-tile twiddle reloads of the FFT warps come from shared-memory copies of the tables.
+  cpx<float>* const tw2s = reinterpret_cast<cpx<float>*>(smem_raw + 2 * kTileBytes + kWork + 2 * kBarBytes);
+  cpx<float>* const twHs = tw2s + NY;
+  cpx<float>* const twNs = twHs + NZ / 2;
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
+    mbar_init(&done[0], kConsumers);
+    mbar_init(&done[1], kConsumers);
+    fence_barrier_init();
+  }
+  for (int q = tid; q < NY; q += kThreads) tw2s[q] = ldg_cpx(p.k2.tw + q);
+  for (int q = tid; q < NZ / 2; q += kThreads) {
+    twHs[q] = ldg_cpx(p.k3.twH + q);
+    twNs[q] = ldg_cpx(p.k3.twN + q);
+  }
+  __syncthreads();
+
+  if (tid >= kConsumers) {
+    if (tid == kConsumers) {
+      tma_prefetch_desc(&map_in);
+      tma_prefetch_desc(&map_out);
+      char* gbase = reinterpret_cast<char*>(p.k3.buf);
+      // planes of the last kSigLag K2 stores, not yet signalled (store completion is only waited
+      // for kSigLag tiles later, so the copy warp never stalls on HBM write latency)
+      constexpr int kSigLag = 4;
+      int pend[kSigLag];
+#pragma unroll
+      for (int q = 0; q < kSigLag; ++q) pend[q] = -1;
+      auto signal = [&](int plane) {
+        if (plane >= 0) {
+          asm volatile("fence.proxy.async;" ::: "memory");
+          asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.plane_done + plane) : "memory");
+        }
+      };
+      auto flush_signals = [&]() {
+        bulk_wait0();
+#pragma unroll
+        for (int q = 0; q < kSigLag; ++q) { signal(pend[q]); pend[q] = -1; }
+      };
+      int cur_type[2], cur_plane[2], cur_idx[2];
+      bool deferred[2] = {false, false};
+      auto plane_ready = [&](int plane) -> bool {
+        unsigned int have;
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(have) : "l"(p.plane_done + plane) : "memory");
+        return have >= (unsigned)p.t2;
+      };
+      auto publish = [&](int b, int type, int plane, int idx) {
+        cur_type[b] = type; cur_plane[b] = plane; cur_idx[b] = idx;
+        desc[4 * b + 0] = type; desc[4 * b + 1] = plane; desc[4 * b + 2] = idx;
+      };
+      // issues the load of the tile published for buffer b.  A K3 tile needs its plane's y pass
+      // complete (`ready` = already known to be).  Non-blocking: returns false if it is not; the
+      // caller retries, blocking, once every earlier tile of this CTA has been stored and
+      // signalled -- see the main loop.
+      auto load = [&](int b, bool blocking, bool ready) -> bool {
+        const int type = cur_type[b], plane = cur_plane[b], idx = cur_idx[b];
+        if (type == kTileEnd) {
+          mbar_arrive(&full[b]);
+        } else if (type == kTileK2) {
+          const int z0 = idx * P2::TZ;
+          mbar_expect_tx(&full[b], (uint32_t)P2::kDenseBytes);
+          for (int r0 = 0; r0 < NY; r0 += p.k2.box_rows) {
+            const int src = r0 / p.k2.rows_per_src, rl = r0 - src * p.k2.rows_per_src;
+            tma_load_4d(dense0 + b * kDenseElems + r0 * P2::TZ, &map_in, &full[b], 2 * z0, rl, plane, src);
+          }
+        } else {
+          if (!ready) ready = plane_ready(plane);
+          if (!ready && !blocking) return false;
+          while (!ready) {
+            __nanosleep(100);
+            ready = plane_ready(plane);
+          }
+          asm volatile("fence.proxy.async;" ::: "memory");
+          const size_t off = ((size_t)plane * p.t3 + idx) * (size_t)P3::kDenseBytes;
+          mbar_expect_tx(&full[b], (uint32_t)P3::kDenseBytes);
+          bulk_g2s(dense0 + b * kDenseElems, gbase + off, (uint32_t)P3::kDenseBytes, &full[b]);
+        }
+        return true;
+      };
+      // static schedule: this CTA owns tickets blockIdx.x + n*gridDim.x, in increasing order
+      unsigned int ticket = blockIdx.x;
+      {
+        int type, plane, idx;
+        k23_decode(p, ticket, type, plane, idx);
+        ticket += gridDim.x;
+        publish(0, type, plane, idx);
+        load(0, true, false);          // nothing of ours is pending: blocking is safe
+        k23_decode(p, ticket, type, plane, idx);
+        ticket += gridDim.x;
+        publish(1, type, plane, idx);
+        deferred[1] = !load(1, false, false);
+      }
+      for (int i = 0;; ++i) {
+        const int b = i & 1;
+        if (cur_type[b] == kTileEnd) break;
+        if (deferred[b]) {
+          // every earlier tile of this CTA has been stored; make that visible, then wait
+          flush_signals();
+          load(b, true, false);
+          deferred[b] = false;
+        }
+        // claim the tile that will replace this one while the FFT warps are still busy with it:
+        // the ticket round trip and the dependency probe stay off the critical path
+        int ntype, nplane, nidx;
+        k23_decode(p, ticket, ntype, nplane, nidx);
+        ticket += gridDim.x;
+        // dependency probe issued now, looked at after the wait below (latency hidden)
+        unsigned int nhave = 0;
+#ifdef RF_EXP_NOSIG
+        nhave = 1u << 30;
+#else
+        if (ntype == kTileK3)
+          asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(nhave) : "l"(p.plane_done + nplane) : "memory");
+#endif
+        mbar_wait(&done[b], (i >> 1) & 1);
+        const bool nready = ntype != kTileK3 || nhave >= (unsigned)p.t2;
+        const int stored_plane = cur_type[b] == kTileK2 ? cur_plane[b] : -1;
+        if (cur_type[b] == kTileK2) {
+          const int z0 = cur_idx[b] * P2::TZ;
+          for (int r0 = 0; r0 < NY; r0 += P2::kBoxRows)
+            tma_store_3d(&map_out, dense0 + b * kDenseElems + r0 * P2::TZ, 2 * z0, r0, cur_plane[b]);
+        } else {
+          const size_t off = ((size_t)cur_plane[b] * p.t3 + cur_idx[b]) * (size_t)P3::kDenseBytes;
+          bulk_s2g(gbase + off, dense0 + b * kDenseElems, (uint32_t)P3::kDenseBytes);
+        }
+        bulk_commit();
+        bulk_wait_read0();
+        publish(b, ntype, nplane, nidx);
+        deferred[b] = !load(b, false, nready);
+        // the store committed kSigLag tiles ago is complete once at most kSigLag groups are pending
+#ifndef RF_EXP_NOSIG
+        asm volatile("cp.async.bulk.wait_group %0;" ::"n"(kSigLag) : "memory");
+        signal(pend[0]);
+#endif
+#pragma unroll
+        for (int q = 0; q + 1 < kSigLag; ++q) pend[q] = pend[q + 1];
+        pend[kSigLag - 1] = stored_plane;
+      }
+      flush_signals();
+    }
+    return;
+  }
+
+  // ===== FFT warps =====
+  double s1 = 0.0, s2 = 0.0;
+  const float* zs = p.k3.zscale;
+  for (int i = 0;; ++i) {
+    const int b = i & 1;
+    cpx<float>* const D = dense0 + b * kDenseElems;
+    mbar_wait(&full[b], (i >> 1) & 1);
+    const int type = desc[4 * b + 0];
+    if (type == kTileEnd) break;
+    if (type == kTileK2) {
+      cpx<float> twr[P2::R1];
+      load_step_twiddles_smem<P2::R1>(twr, tw2s, tid / P2::TZ);
+      k2_tile_body<NY>(D, work, tid, twr);
+    } else {
+      cpx<float> twr[P3::R1];
+      cpx<float> twu[K3Consts<NZ>::kPairsPerThread];
+      sfor<0, K3Consts<NZ>::kPairsPerThread>([&](auto qi) {
+        constexpr int q = decltype(qi)::value;
+        twu[q] = ld_cpx(twNs + (tid + q * kConsumers) % (P3::H / 2));
+      });
+      load_step_twiddles_smem<P3::R1>(twr, twHs, tid % P3::M);
+      float a1 = 0.f, a2 = 0.f;
+      k3_tile_body<NZ>(D, work, tid, twr, twu, zs, a1, a2);
+      s1 += (double)a1;
+      s2 += (double)a2;
+    }
+    fence_proxy_async();
+    mbar_arrive(&done[b]);
+    ConsumerSync()();
+  }
+
+  if (p.k3.partials) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    __shared__ double red[2][kConsumers / 32];
+    const int wid = tid >> 5, lane = tid & 31;
+    if (lane == 0) { red[0][wid] = s1; red[1][wid] = s2; }
+    ConsumerSync()();
+    if (tid == 0) {
+      double t1 = 0, t2 = 0;
+      for (int q = 0; q < kConsumers / 32; ++q) { t1 += red[0][q]; t2 += red[1][q]; }
+      p.k3.partials[2 * (size_t)blockIdx.x] = t1;
+      p.k3.partials[2 * (size_t)blockIdx.x + 1] = t2;
+    }
+  }
 }
 
 // @@PIPE_END@@

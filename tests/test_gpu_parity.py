@@ -171,3 +171,67 @@ def test_potential_regeneration(lib):
     scale = np.sqrt(np.mean(np.abs(want) ** 2))
     assert np.sqrt(np.mean(np.abs(pot - want) ** 2)) <= 1e-6 * scale
     assert pot[0, 0, 0] == 0
+
+
+# ------------------------------------------------------------------------------------------
+# gate 4: statistics of the Philox field
+# ------------------------------------------------------------------------------------------
+def test_gaussian_variance_kat_gpu(lib):
+    """The reference's known-answer test (tests/test_generate.py:24-62) on the GPU Philox path:
+    Gaussian P(k) = P0 exp(-(k sigma)^2/2); mean variance within 1 % of the analytic value.  The
+    reference averages its 10 MT19937 seeds (scatter of the mean ~1 %, it passes at 0.25 %); the
+    Philox stream is a different sample, so 200 seeds are averaged (scatter ~0.2 %) to make the
+    same 1 % gate a 4-sigma statement."""
+    from scipy.special import erf
+    spacing, n, seed = 2.5, 64, 123
+    kmin, kmax = (2 * np.pi) / (spacing * n), np.pi / spacing
+    sigma, P0 = 2.5 * spacing, 1.23
+    calc = P0 / (2 * np.pi) ** 1.5 / sigma ** 3 * (
+        erf(kmax * sigma / np.sqrt(2)) ** 3 - erf(kmin * sigma / np.sqrt(2)) ** 3)
+    power = np.empty(100, dtype=[('k', float), ('Pk', float)])
+    power['k'] = np.linspace(kmin, np.sqrt(3) * kmax, len(power))
+    power['Pk'] = P0 * np.exp(-0.5 * (power['k'] * sigma) ** 2)
+    eng = _engine(lib, (n, n, n), spacing, power)
+    var = []
+    for t in range(200):
+        eng.generate_delta(seed + t, want_stats=True)
+        s1, s2, cnt = eng.stats()
+        var.append(s2 / cnt - (s1 / cnt) ** 2)
+        if t < 3:
+            assert abs(var[-1] - np.var(eng.copy_field().astype(np.float64))) < 1e-5 * var[-1]
+    assert abs(np.mean(var) - calc) < 0.01 * calc
+
+
+def test_power_spectrum_recovered(lib):
+    """Measured P(k) of the generated field recovers the input spectrum within cosmic
+    variance: |delta_k|^2 V / N^6 averaged over shells of N_modes modes scatters around P(k)
+    with relative std 1/sqrt(N_modes)."""
+    shape, spacing, seed = (128, 128, 128), 2.0, 2025
+    power = oracle.load_default_power()
+    eng = _engine(lib, shape, spacing, power)
+    eng.generate_delta(seed)
+    delta = eng.copy_field().astype(np.float64)
+    nx, ny, nz = shape
+    N3 = nx * ny * nz
+    V = N3 * spacing ** 3
+    dk = np.fft.rfftn(delta)
+    kx2, ky2, kz2 = oracle.create_ksq_grids(shape, spacing, packed=True)
+    k = np.sqrt(kx2 + ky2 + kz2)
+    pk_in = np.interp(np.log10(np.where(k > 0, k, 1.0)), np.log10(power['k']), power['Pk'])
+    ratio = (np.abs(dk) ** 2 * V / N3 ** 2) / pk_in
+    # interior planes only: modes there are independent complex Gaussians (no Hermitian pairs)
+    sel = np.zeros(k.shape, dtype=bool)
+    sel[:, :, 1:nz // 2] = True
+    edges = np.linspace(k[sel].min(), k[sel].max(), 25)
+    which = np.digitize(k[sel], edges)
+    r = ratio[sel]
+    worst = 0.0
+    for b in range(1, len(edges)):
+        m = which == b
+        nm = int(m.sum())
+        if nm < 50:
+            continue
+        dev = abs(r[m].mean() - 1.0) * np.sqrt(nm)
+        worst = max(worst, dev)
+    assert worst < 5.0, worst
+    assert abs(r.mean() - 1.0) < 5.0 / np.sqrt(r.size)
