@@ -18,7 +18,7 @@ BUILD = os.path.join(CSRC, "build")
 LIB = os.path.join(HERE, "librf_b200.so")
 
 SIZES = (64, 128, 256, 512, 1024, 2048, 4096)
-PIPE_SIZES = (64, 128, 256, 512, 1024, 2048)
+PIPE_SIZES = (64, 128, 256, 512, 1024, 2048, 4096)
 DTYPES = (("f32", "float"), ("f64", "double"))
 
 NVCC_FLAGS = [

@@ -484,6 +484,7 @@ static int ensure_partials(rf_ctx* c, long long n) {
     case 512: { constexpr int NN = 512; __VA_ARGS__; } break;  \
     case 1024: { constexpr int NN = 1024; __VA_ARGS__; } break;\
     case 2048: { constexpr int NN = 2048; __VA_ARGS__; } break;\
+    case 4096: { constexpr int NN = 4096; __VA_ARGS__; } break;\
     default: return fail(RF_ERR_ARG, "size not compiled");\
   }
 
@@ -735,7 +736,7 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
     }
     bool done3 = fused_done;
     if constexpr (std::is_same<T, float>::value) {
-      if (!fused_done && c->pipe && c->nz <= 2048) {
+      if (!fused_done && c->pipe && c->nz <= 4096) {
         pipe::K3PParams q;
         q.buf = (float*)c->field;
         q.twH = (const cpx<float>*)c->tw_zh;

@@ -142,14 +142,19 @@ struct LayoutStridedPad {
 // every M = H/R1 elements
 template <int NZ>
 struct LPlan;
+// H = complex line length (NZ/2).  The FFT engine runs on HE = H / SPLIT points: for NZ = 4096
+// a radix-2 DIF stage in shared memory splits each line into two independent half-lines
+// (even / odd outputs), so the two-step radix-32 engine still applies.
 #define RF_LPLAN2(NN, A, B)                                  \
   template <>                                                \
   struct LPlan<NN> {                                         \
-    static constexpr int H = NN / 2, R1 = A, R2 = B, M = H / A; \
+    static constexpr int H = NN / 2, R1 = A, R2 = B;         \
+    static constexpr int HE = A * B, SPLIT = H / HE, M = HE / A; \
     static constexpr int TL = 8192 / H;                      \
-    static constexpr int WP = H + A;                         \
+    static constexpr int TE = TL * SPLIT;                    \
+    static constexpr int WP = HE + A;                        \
     static constexpr int kDenseBytes = TL * H * 8;           \
-    static constexpr int kWorkBytes = TL * WP * 8;           \
+    static constexpr int kWorkBytes = TE * WP * 8;           \
   };
 RF_LPLAN2(64, 8, 4)
 RF_LPLAN2(128, 8, 8)
@@ -157,6 +162,7 @@ RF_LPLAN2(256, 16, 8)
 RF_LPLAN2(512, 16, 16)
 RF_LPLAN2(1024, 16, 32)
 RF_LPLAN2(2048, 32, 32)
+RF_LPLAN2(4096, 32, 32)
 #undef RF_LPLAN2
 
 template <int WP, int M>
@@ -212,11 +218,11 @@ __device__ __forceinline__ void step_b(const cpx<float>* __restrict__ work, int 
   }
 }
 // the step-A twiddles of this thread: W_N^(j*k1), k1 < R1
-template <int R1>
+template <int R1, int STRIDE = 1>
 __device__ __forceinline__ void load_step_twiddles(cpx<float> (&twr)[R1], const cpx<float>* tw, int j) {
   sfor<0, R1>([&](auto ki) {
     constexpr int k1 = decltype(ki)::value;
-    twr[k1] = ldg_cpx(tw + j * k1);
+    twr[k1] = ldg_cpx(tw + j * k1 * STRIDE);
   });
 }
 
@@ -248,15 +254,18 @@ __device__ __forceinline__ void k3_load_twiddles(cpx<float> (&twr)[LPlan<NZ>::R1
     constexpr int q = decltype(qi)::value;
     twu[q] = ldg_cpx(twN + (tid + q * kConsumers) % (H / 2));
   });
-  load_step_twiddles<LPlan<NZ>::R1>(twr, twH, tid % LPlan<NZ>::M);
+  // table twH holds W_H^k; the engine needs W_HE^(j*k1) = W_H^(SPLIT*j*k1)
+  load_step_twiddles<LPlan<NZ>::R1, LPlan<NZ>::SPLIT>(twr, twH, tid % LPlan<NZ>::M);
 }
 template <int NZ>
 __device__ __forceinline__ void k3_tile_body(cpx<float>* __restrict__ D, cpx<float>* __restrict__ work, int tid,
                                              const cpx<float> (&twr)[LPlan<NZ>::R1],
                                              const cpx<float> (&twu)[K3Consts<NZ>::kPairsPerThread],
-                                             const float* zs, float& a1, float& a2) {
+                                             const float* zs, float& a1, float& a2,
+                                             const cpx<float>* twH = nullptr) {
   using P = LPlan<NZ>;
   constexpr int H = P::H;
+  constexpr int HE = P::HE;
   constexpr int kPairsPerThread = K3Consts<NZ>::kPairsPerThread;
   using L = LayoutLinesPad<P::WP, P::M>;
   static_assert(kConsumers % (H / 2) == 0 || (H / 2) % kConsumers == 0, "unpack mapping");
@@ -305,23 +314,40 @@ __device__ __forceinline__ void k3_tile_body(cpx<float>* __restrict__ D, cpx<flo
     }
     ConsumerSync()();
 
-    step_a<H, P::R1, L>(work, tid, P::TL, twr, [&](cpx<float>(&v)[P::R1], int j, int l) {
-      const cpx<float>* Lp = D + l * H + j;
+    if constexpr (P::SPLIT == 2) {
+      // radix-2 DIF across the two halves of every line, in place:
+      //   first half <- Z[k] + Z[k+H/2] (even outputs), second half <- (Z[k] - Z[k+H/2]) W_H^k (odd)
+      for (int w = tid; w < P::TL * (H / 2); w += kConsumers) {
+        const int l = w / (H / 2), k = w % (H / 2);
+        cpx<float>* Lp = D + l * H + k;
+        cpx<float> a = Lp[0], c = Lp[H / 2];
+        cpx<float> tw = ldg_cpx(twH + k);
+        Lp[0] = a + c;
+        Lp[H / 2] = cmul(a - c, tw);
+      }
+      ConsumerSync()();
+    }
+    // the tile is now TE = TL*SPLIT independent lines of HE points, contiguous in D
+    step_a<HE, P::R1, L>(work, tid, P::TE, twr, [&](cpx<float>(&v)[P::R1], int j, int l) {
+      const cpx<float>* Lp = D + l * HE + j;
       sfor<0, P::R1>([&](auto mi) {
         constexpr int m = decltype(mi)::value;
         v[m] = ld_cpx(Lp + P::M * m);
       });
     });
     ConsumerSync()();
-    step_b<H, P::R1, L>(work, tid, P::TL, [&](int k, int l, cpx<float> x) {
+    step_b<HE, P::R1, L>(work, tid, P::TE, [&](int k, int l, cpx<float> x) {
       a1 += x.x + x.y;
       a2 = fmaf(x.x, x.x, fmaf(x.y, x.y, a2));
+      // engine line l = SPLIT*line + parity holds outputs parity, parity + SPLIT, ...
+      const int pos = P::SPLIT == 1 ? k : P::SPLIT * k + (l % P::SPLIT);
+      const int line = l / P::SPLIT;
       if (zs) {
-        float2 z = __ldg(reinterpret_cast<const float2*>(zs) + k);
+        float2 z = __ldg(reinterpret_cast<const float2*>(zs) + pos);
         x.x *= z.x;
         x.y *= z.y;
       }
-      st_cpx(D + l * H + k, x);
+      st_cpx(D + line * H + pos, x);
     });
 }
 
@@ -409,7 +435,7 @@ __global__ void __launch_bounds__(kThreads, 1) k3p_c2r_lines(const K3PParams p) 
     mbar_wait(&full[b], (i >> 1) & 1);
 
     float a1 = 0.f, a2 = 0.f;
-    k3_tile_body<NZ>(D, work, tid, twr, twu, zs, a1, a2);
+    k3_tile_body<NZ>(D, work, tid, twr, twu, zs, a1, a2, p.twH);
     s1 += (double)a1;
     s2 += (double)a2;
     fence_proxy_async();
@@ -887,9 +913,9 @@ k23p_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant_
         constexpr int q = decltype(qi)::value;
         twu[q] = ld_cpx(twNs + (tid + q * kConsumers) % (P3::H / 2));
       });
-      load_step_twiddles_smem<P3::R1>(twr, twHs, tid % P3::M);
+      load_step_twiddles_smem<P3::R1>(twr, twHs, tid % P3::M);   // (NZ <= 2048 here: SPLIT == 1)
       float a1 = 0.f, a2 = 0.f;
-      k3_tile_body<NZ>(D, work, tid, twr, twu, zs, a1, a2);
+      k3_tile_body<NZ>(D, work, tid, twr, twu, zs, a1, a2, p.k3.twH);
       s1 += (double)a1;
       s2 += (double)a2;
     }
