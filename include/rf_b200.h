@@ -128,6 +128,19 @@ void rf_host_free(void* p);
 int rf_set_timing(rf_ctx* ctx, int enabled);
 int rf_get_timing(rf_ctx* ctx, double* ms_pass1, double* ms_pass2, double* ms_pass3);
 
+/* Direct exchange (slab decomposition, 2..8 ranks of one box): pass 1 stores every x line
+ * straight into the receive buffers of the ranks that own each x range, over NVLink peer
+ * memory, so the all-to-all is part of rf_generate_xpass (no send buffer, no separate
+ * collective).  Set every rank's RF_BUF_RECV pointer with rf_set_peer_recv (same process: the
+ * pointer itself; other processes: rf_ipc_export on the owner, rf_ipc_open here), then
+ * rf_set_direct(ctx, 1).  The caller still synchronises the ranks before and after pass 1
+ * (peers must have finished reading / writing the receive buffers). */
+int rf_ipc_export(rf_ctx* ctx, int which, unsigned char* handle64);
+int rf_ipc_open(const unsigned char* handle64, void** ptr);
+int rf_ipc_close(void* ptr);
+int rf_set_peer_recv(rf_ctx* ctx, int rank, void* recv_ptr);
+int rf_set_direct(rf_ctx* ctx, int enabled);
+
 /* raw device pointers for zero-copy wrapping (torch / DLPack) and for the all-to-all */
 void* rf_device_ptr(rf_ctx* ctx, int which);
 long long rf_buffer_bytes(rf_ctx* ctx, int which);

@@ -49,6 +49,11 @@ SIGNATURES = {
     "rf_get_timing": (_c.c_int, [_P, _c.POINTER(_c.c_double), _c.POINTER(_c.c_double), _c.POINTER(_c.c_double)]),
     "rf_device_ptr": (_P, [_P, _c.c_int]),
     "rf_buffer_bytes": (_c.c_longlong, [_P, _c.c_int]),
+    "rf_ipc_export": (_c.c_int, [_P, _c.c_int, _P]),
+    "rf_ipc_open": (_c.c_int, [_P, _c.POINTER(_P)]),
+    "rf_ipc_close": (_c.c_int, [_P]),
+    "rf_set_peer_recv": (_c.c_int, [_P, _c.c_int, _P]),
+    "rf_set_direct": (_c.c_int, [_P, _c.c_int]),
     "rf_is_fast": (_c.c_int, [_P]),
     "rf_is_pipelined": (_c.c_int, [_P]),
     "rf_launch_count": (_c.c_longlong, [_P]),
@@ -228,6 +233,25 @@ class Engine:
 
     def buffer_bytes(self, which=RF_BUF_FIELD):
         return lib().rf_buffer_bytes(self._ctx, which)
+
+    # -- direct exchange over peer memory ---------------------------------------------------
+    def ipc_export(self, which=RF_BUF_RECV):
+        buf = ctypes.create_string_buffer(64)
+        check(lib().rf_ipc_export(self._ctx, which, ctypes.cast(buf, ctypes.c_void_p)), value_error_ok=False)
+        return bytes(buf.raw)
+
+    @staticmethod
+    def ipc_open(handle):
+        buf = ctypes.create_string_buffer(bytes(handle), 64)
+        out = ctypes.c_void_p()
+        check(lib().rf_ipc_open(ctypes.cast(buf, ctypes.c_void_p), ctypes.byref(out)), value_error_ok=False)
+        return out.value
+
+    def set_peer_recv(self, rank, ptr):
+        check(lib().rf_set_peer_recv(self._ctx, int(rank), ctypes.c_void_p(ptr)))
+
+    def set_direct(self, enabled=True):
+        check(lib().rf_set_direct(self._ctx, int(bool(enabled))))
 
     @property
     def is_fast(self):

@@ -42,6 +42,8 @@ struct rf_ctx {
   bool pipe = false;        // TMA-pipelined kernels (f32, env RF_PIPE != 0)
   bool fuse = false;        // fused y+z kernel k23p (env RF_FUSE != 0)
   unsigned int* sched = nullptr;   // [1 + nxl] ticket + per-plane counters of k23p
+  void* peer_recv[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  bool direct = false;      // pass 1 stores straight into the peers' receive buffers
   int num_sms = 148;
   size_t esize = 4;         // sizeof(T)
   cudaStream_t own_stream = nullptr, stream = nullptr;
@@ -204,6 +206,49 @@ extern "C" int rf_get_timing(rf_ctx* c, double* a, double* b, double* d) {
   if (d) *d = t[2];
   return RF_OK;
 }
+// ------------------------------------------------------------------------------------------
+// direct exchange over peer memory
+// ------------------------------------------------------------------------------------------
+extern "C" int rf_ipc_export(rf_ctx* c, int which, unsigned char* handle64) {
+  if (!c || !handle64) return fail(RF_ERR_ARG, "rf_ipc_export: null argument");
+  void* p = rf_device_ptr(c, which);
+  if (!p) return fail(RF_ERR_STATE, "rf_ipc_export: buffer not allocated");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+  cudaIpcMemHandle_t h;
+  RF_CUDA(cudaIpcGetMemHandle(&h, p));
+  memcpy(handle64, &h, 64);
+  return RF_OK;
+}
+extern "C" int rf_ipc_open(const unsigned char* handle64, void** ptr) {
+  if (!handle64 || !ptr) return fail(RF_ERR_ARG, "rf_ipc_open: null argument");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  RF_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return RF_OK;
+}
+extern "C" int rf_ipc_close(void* ptr) {
+  if (ptr) RF_CUDA(cudaIpcCloseMemHandle(ptr));
+  return RF_OK;
+}
+extern "C" int rf_set_peer_recv(rf_ctx* c, int rank, void* recv_ptr) {
+  if (!c || rank < 0 || rank >= c->world || c->world > 8)
+    return fail(RF_ERR_ARG, "rf_set_peer_recv: bad rank (direct exchange supports up to 8 ranks)");
+  c->peer_recv[rank] = recv_ptr;
+  return RF_OK;
+}
+extern "C" int rf_set_direct(rf_ctx* c, int enabled) {
+  if (!c) return fail(RF_ERR_ARG, "null ctx");
+  if (enabled) {
+    if (c->world < 2 || c->world > 8 || !is_pow2(c->nxl))
+      return fail(RF_ERR_ARG, "rf_set_direct: needs 2..8 ranks and a power-of-two x-slab");
+    c->peer_recv[c->rank] = c->recv;
+    for (int r = 0; r < c->world; ++r)
+      if (!c->peer_recv[r]) return fail(RF_ERR_STATE, "rf_set_direct: a peer receive buffer is not set");
+  }
+  c->direct = enabled != 0;
+  return RF_OK;
+}
+
 extern "C" int rf_is_fast(rf_ctx* c) { return c && c->fast ? 1 : 0; }
 extern "C" int rf_is_pipelined(rf_ctx* c) {
   return c && c->pipe && c->nx <= 1024 && c->ny <= 1024 && c->nz <= 2048 ? 1 : 0;
@@ -556,16 +601,30 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
       }
       q.plane = (const cpx<float>*)c->plane;
       int e = 0;
-      CUtensorMap mout;
+      pipe::K1PMaps mout;
+      memset(&mout, 0, sizeof(mout));
       RF_DISPATCH_PIPE1K(c->nx, {
         const int tz = PipeLaunch<NN>::tile_cols();
         q.ztiles = nzc / tz;
         q.ntiles = c->nyl * q.ztiles;
-        uint64_t dout[3] = {(uint64_t)2 * nzc, (uint64_t)c->nyl, (uint64_t)c->nx};
         uint64_t sout[2] = {(uint64_t)nzc * 8, (uint64_t)c->nyl * nzc * 8};
-        uint32_t bout[3] = {(uint32_t)2 * tz, 1, (uint32_t)PipeLaunch<NN>::box_rows()};
-        int e2 = make_tensor_map(&mout, c->field, 3, dout, sout, bout);
-        if (e2) return e2;
+        if (c->direct) {
+          // one map per destination: this rank's source block in that rank's receive buffer
+          q.nxl = c->nxl;
+          uint64_t dout[3] = {(uint64_t)2 * nzc, (uint64_t)c->nyl, (uint64_t)c->nxl};
+          uint32_t bout[3] = {(uint32_t)2 * tz, 1, (uint32_t)std::min(PipeLaunch<NN>::box_rows(), c->nxl)};
+          const size_t block = (size_t)c->nxl * c->nyl * nzc * sizeof(cpx<float>);
+          for (int d = 0; d < c->world; ++d) {
+            int e2 = make_tensor_map(&mout.m[d], (char*)c->peer_recv[d] + (size_t)c->rank * block, 3, dout, sout, bout);
+            if (e2) return e2;
+          }
+        } else {
+          q.nxl = c->nx;
+          uint64_t dout[3] = {(uint64_t)2 * nzc, (uint64_t)c->nyl, (uint64_t)c->nx};
+          uint32_t bout[3] = {(uint32_t)2 * tz, 1, (uint32_t)PipeLaunch<NN>::box_rows()};
+          int e2 = make_tensor_map(&mout.m[0], c->field, 3, dout, sout, bout);
+          if (e2) return e2;
+        }
         int grid = std::min(q.ntiles, c->num_sms);
         mark(c, 0);
         e = PipeLaunch<NN>::k1p(c->noise != nullptr, potential != 0, mout, q, grid, c->stream);
@@ -580,6 +639,14 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
     K1Params<T> p;
     p.geom = g; p.tab = tab; p.out = (cpx<T>*)c->field; p.tw = (const cpx<T>*)c->tw_x;
     p.ny_local = c->nyl; p.y0 = c->rank * c->nyl;
+    p.direct = c->direct ? 1 : 0;
+    p.nxl_shift = 0;
+    for (int d = 0; d < 8; ++d) p.peer[d] = nullptr;
+    if (c->direct) {
+      while ((1 << p.nxl_shift) < c->nxl) ++p.nxl_shift;
+      const size_t block = (size_t)c->nxl * c->nyl * (c->nz / 2);
+      for (int d = 0; d < c->world; ++d) p.peer[d] = (cpx<T>*)c->peer_recv[d] + (size_t)c->rank * block;
+    }
     int e = 0;
     RF_DISPATCH_N(c->nx, {
       int grid = c->nyl * ((c->nz / 2) / FftPlan<T, NN>::TZ);

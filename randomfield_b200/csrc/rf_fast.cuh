@@ -228,6 +228,12 @@ struct K1Params {
   cpx<T>* out;            // [nx][ny_local][nz/2]
   const cpx<T>* tw;       // exp(+2 pi i k / nx), k < nx
   int ny_local, y0;       // y-slab owned by this rank (multi-GPU); y0 = first global iy
+  // direct exchange (slab decomposition over peer memory): the x line is scattered straight
+  // into the receive buffers of the ranks that own each x range.  peer[d] points at this
+  // rank's source block [nx/G][ny_local][nz/2] inside rank d's receive buffer (peer[own] is
+  // local memory); nxl_shift = log2(nx/G).  direct == 0: store to `out`.
+  cpx<T>* peer[8];
+  int direct, nxl_shift;
 };
 
 template <typename T, int NX, bool INJ>
@@ -291,6 +297,15 @@ k1_generate_xfft(const K1Params<T> p) {
   };
   cpx<T>* outp = p.out + (size_t)iyl * nzc + z0;
   const size_t xstride = (size_t)p.ny_local * nzc;
+  if (p.direct) {
+    const int shift = p.nxl_shift, mask = (1 << shift) - 1;
+    const size_t col = (size_t)iyl * nzc + z0;
+    auto storeP = [&](int k, int c, cpx<T> x) {
+      st_cpx(p.peer[k >> shift] + (size_t)(k & mask) * xstride + col + c, x);
+    };
+    tile_fft<T, NX, P::R1, P::R2, P::R3, P::NT, true, L>(sm, p.tw, P::TZ, loadA, storeP);
+    return;
+  }
   auto storeF = [&](int k, int c, cpx<T> x) { st_cpx(outp + (size_t)k * xstride + c, x); };
   tile_fft<T, NX, P::R1, P::R2, P::R3, P::NT, true, L>(sm, p.tw, P::TZ, loadA, storeF);
 }

@@ -24,7 +24,7 @@ struct PipeLaunch {
   // N <= 1024 only
   static int k2p(const CUtensorMap& in, const CUtensorMap& out, const pipe::K2PParams& p, int grid,
                  cudaStream_t s);
-  static int k1p(bool injected, bool potential, const CUtensorMap& out, const pipe::K1PParams& p, int grid, cudaStream_t s);
+  static int k1p(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s);
   // fused y + z pass (this N = ny); nz in 64..2048
   static int k23p(int nz, const CUtensorMap& in, const CUtensorMap& out, const pipe::K23Params& p, int grid,
                   cudaStream_t s);

@@ -588,6 +588,14 @@ struct K1PParams {
   const cpx<float>* plane; // [nx][ny_local] packed iz = 0 / nz/2 column (gen_packed_plane_kernel)
   int ny_local, y0;        // y-slab owned by this rank; y0 = first global iy
   int ntiles, ztiles;      // ny_local * ztiles, (nz/2) / TZ
+  int nxl;                 // rows per destination rank (== NX when not slab-decomposed)
+};
+
+// one store map per destination rank: (2*ncols floats, ny_local, nx/G) over this rank's source
+// block in that rank's receive buffer (peer memory over NVLink; the own block is local).
+// Without slab decomposition maps[0] is the field buffer itself.
+struct alignas(64) K1PMaps {
+  CUtensorMap m[8];
 };
 
 template <int NX>
@@ -600,7 +608,7 @@ constexpr int k1p_smem_bytes() {
 // stores after step B and, two tiles later, checks that they have drained the buffer.
 template <int NX, bool INJ, bool POT>
 __global__ void __launch_bounds__(kConsumers, 1)
-k1p_generate_xfft(const __grid_constant__ CUtensorMap map_out, const K1PParams p) {
+k1p_generate_xfft(const __grid_constant__ K1PMaps maps, const K1PParams p) {
   using P = SPlan<NX>;
   using L = LayoutStridedPad<P::TZ, P::M>;
   static_assert(P::M * P::TZ == kConsumers, "one step-A item per thread");
@@ -610,7 +618,7 @@ k1p_generate_xfft(const __grid_constant__ CUtensorMap map_out, const K1PParams p
   cpx<float>* const work = reinterpret_cast<cpx<float>*>(smem_raw + 2 * P::kDenseBytes);
   const int tid = threadIdx.x;
   const int first = blockIdx.x, step = gridDim.x;
-  if (tid == 0) tma_prefetch_desc(&map_out);
+  if (tid == 0) tma_prefetch_desc(&maps.m[0]);
 
   const ModeGeom<float>& g = p.geom;
   const int c = tid % P::TZ, j = tid / P::TZ;
@@ -673,8 +681,12 @@ k1p_generate_xfft(const __grid_constant__ CUtensorMap map_out, const K1PParams p
     fence_proxy_async();
     __syncthreads();
     if (tid == 0) {
-      for (int r0 = 0; r0 < NX; r0 += P::kBoxRows)
-        tma_store_3d(&map_out, D + r0 * P::TZ, 2 * z0, iyl, r0);
+      // boxes never straddle two destinations (box rows = min(256, nxl), both powers of two)
+      const int box = p.nxl < P::kBoxRows ? p.nxl : P::kBoxRows;
+      for (int r0 = 0; r0 < NX; r0 += box) {
+        const int d = r0 / p.nxl;
+        tma_store_3d(&maps.m[d], D + r0 * P::TZ, 2 * z0, iyl, r0 - d * p.nxl);
+      }
       bulk_commit();
     }
   }

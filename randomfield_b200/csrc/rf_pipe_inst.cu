@@ -39,7 +39,7 @@ int PipeLaunch<N>::k2p(const CUtensorMap& in, const CUtensorMap& out, const pipe
   return (int)cudaGetLastError();
 }
 template <bool INJ, bool POT>
-static int launch_k1p(const CUtensorMap& out, const pipe::K1PParams& p, int grid, cudaStream_t s) {
+static int launch_k1p(const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s) {
   constexpr int smem = pipe::k1p_smem_bytes<N>();
   int e;
   if ((e = set_smem_pipe(pipe::k1p_generate_xfft<N, INJ, POT>, smem))) return e;
@@ -47,7 +47,7 @@ static int launch_k1p(const CUtensorMap& out, const pipe::K1PParams& p, int grid
   return (int)cudaGetLastError();
 }
 template <>
-int PipeLaunch<N>::k1p(bool injected, bool potential, const CUtensorMap& out, const pipe::K1PParams& p,
+int PipeLaunch<N>::k1p(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p,
                        int grid, cudaStream_t s) {
   if (injected) return potential ? launch_k1p<true, true>(out, p, grid, s) : launch_k1p<true, false>(out, p, grid, s);
   return potential ? launch_k1p<false, true>(out, p, grid, s) : launch_k1p<false, false>(out, p, grid, s);

@@ -13,6 +13,8 @@ Buffer layouts (complex elements, nzc = nz/2):
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 
 from . import _lib
@@ -49,7 +51,8 @@ def all_to_all(send, recv, group=None):
 class SlabEngine(object):
     """The device side of a slab-decomposed Generator on this rank."""
 
-    def __init__(self, nx, ny, nz, spacing, power, smoothing=0.0, dtype=np.float32, group=None):
+    def __init__(self, nx, ny, nz, spacing, power, smoothing=0.0, dtype=np.float32, group=None,
+                 direct=None):
         import torch
         import torch.distributed as dist
         self.group = group
@@ -66,10 +69,27 @@ class SlabEngine(object):
         if self.world > 1:
             self._send = self.engine.torch_view(_lib.RF_BUF_FIELD, self._xfer_bytes)
             self._recv = self.engine.torch_view(_lib.RF_BUF_RECV, self._xfer_bytes)
+        # direct exchange: pass 1 stores into the peers' receive buffers over NVLink (CUDA IPC
+        # mappings), the all-to-all disappears; two tiny all-reduces fence the receive buffers
+        if direct is None:
+            direct = os.environ.get("RF_DIRECT", "1") != "0"
+        self.direct = bool(direct) and 2 <= self.world <= 8
+        self._peer_ptrs = []
+        if self.direct:
+            handles = [None] * self.world
+            dist.all_gather_object(handles, self.engine.ipc_export(_lib.RF_BUF_RECV), group=group)
+            for r, h in enumerate(handles):
+                if r == self.rank:
+                    continue
+                ptr = _lib.Engine.ipc_open(h)
+                self._peer_ptrs.append(ptr)
+                self.engine.set_peer_recv(r, ptr)
+            self.engine.set_direct(True)
+            self._fence = torch.zeros(1, device="cuda")
 
     @property
     def exchange_bytes(self):
-        """Bytes this rank sends to other ranks per step."""
+        """Bytes this rank sends to other ranks per step (NVLink, either mode)."""
         return self._xfer_bytes * (self.world - 1) // self.world
 
     def generate(self, seed, potential=False, zscale=None, want_stats=True):
@@ -79,8 +99,15 @@ class SlabEngine(object):
             if self.world == 1:
                 self.engine.generate_delta(seed, potential, zscale, want_stats)
             else:
-                self.engine.generate_xpass(seed, potential)
-                all_to_all(self._send, self._recv, self.group)
+                if self.direct:
+                    # peers have finished reading their receive buffers (previous step) ...
+                    dist.all_reduce(self._fence, group=self.group)
+                    self.engine.generate_xpass(seed, potential)
+                    # ... and every rank's pass-1 stores have landed before anyone reads
+                    dist.all_reduce(self._fence, group=self.group)
+                else:
+                    self.engine.generate_xpass(seed, potential)
+                    all_to_all(self._send, self._recv, self.group)
                 self.engine.finish_yz(zscale, want_stats)
 
     def global_stats(self):
@@ -100,7 +127,7 @@ class SlabEngine(object):
 
 
 def run_virtual_slabs(nx, ny, nz, spacing, power, seed, world, smoothing=0.0, dtype=np.float32,
-                      potential=False, zscale=None):
+                      potential=False, zscale=None, direct=False):
     """All `world` ranks of the slab pipeline driven from ONE process on ONE GPU: each rank's
     engine generates its y-slab, the all-to-all is done with device copies between the
     engines' buffers, each rank finishes its x-slab.  Returns (field (nx, ny, nz), mean, std).
@@ -111,11 +138,16 @@ def run_virtual_slabs(nx, ny, nz, spacing, power, seed, world, smoothing=0.0, dt
     engines = [_lib.Engine(nx, ny, nz, dtype=dtype, rank=r, world=world) for r in range(world)]
     itemsize = engines[0].complex_dtype.itemsize
     xfer = nx * (ny // world) * (nz // 2) * itemsize
+    if direct and world > 1:
+        for e in engines:
+            for r, peer in enumerate(engines):
+                e.set_peer_recv(r, peer.device_ptr(_lib.RF_BUF_RECV))
+            e.set_direct(True)
     for e in engines:
         e.set_power(k, sig, spacing)
         e.generate_xpass(seed, potential)
         e.sync()
-    if world > 1:
+    if world > 1 and not direct:
         sends = [e.torch_view(_lib.RF_BUF_FIELD, xfer).view(world, -1) for e in engines]
         recvs = [e.torch_view(_lib.RF_BUF_RECV, xfer).view(world, -1) for e in engines]
         for d in range(world):

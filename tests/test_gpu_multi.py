@@ -27,6 +27,18 @@ def test_field_bit_identical_across_decompositions(shape):
         assert abs(std - std1) <= 1e-9 * std1
 
 
+@pytest.mark.parametrize("shape", [(64, 64, 64), (256, 128, 128)])
+def test_direct_exchange_bit_identical(shape):
+    """Pass 1 storing straight into the receive buffers of the owning ranks (peer memory; here
+    all ranks live on one GPU) gives the same bits as the all-to-all path."""
+    from randomfield_b200 import slab
+    power = oracle.load_default_power()
+    ref, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=99, world=1)
+    for world in (2, 4, 8):
+        got, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=99, world=world, direct=True)
+        assert np.array_equal(got, ref), "world=%d" % world
+
+
 def test_slab_field_matches_oracle():
     """and the decomposed field is the right field: Philox restatement + numpy irfftn."""
     from randomfield_b200 import slab
