@@ -41,6 +41,7 @@ struct rf_ctx {
   bool fast = false;
   bool pipe = false;        // TMA-pipelined kernels (f32, env RF_PIPE != 0)
   bool fuse = false;        // fused y+z kernel k23p (env RF_FUSE != 0)
+  bool k1q = true;          // pass 1 with two CTAs per SM (env RF_K1Q=0: one-CTA k1p)
   unsigned int* sched = nullptr;   // [1 + nxl] ticket + per-plane counters of k23p
   void* peer_recv[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   bool direct = false;      // pass 1 stores straight into the peers' receive buffers
@@ -126,6 +127,8 @@ extern "C" int rf_create(int nx, int ny, int nz, int dtype, int rank, int world,
     const char* envf = getenv("RF_FUSE");
     // opt-in: measured slower than k2p + k3p on B200, kept for the L2-reuse work
     c->fuse = c->pipe && ny <= 1024 && nz <= 2048 && envf && envf[0] == '1';
+    const char* envq = getenv("RF_K1Q");
+    c->k1q = !(envq && envq[0] == '0');
   }
   RF_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
   c->stream = c->own_stream;
@@ -625,9 +628,11 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
           int e2 = make_tensor_map(&mout.m[0], c->field, 3, dout, sout, bout);
           if (e2) return e2;
         }
-        int grid = std::min(q.ntiles, c->num_sms);
+        const bool twocta = c->k1q && PipeLaunch<NN>::k1q_fits(c->lut_n);
+        int grid = std::min(q.ntiles, (twocta ? 2 : 1) * c->num_sms);
         mark(c, 0);
-        e = PipeLaunch<NN>::k1p(c->noise != nullptr, potential != 0, mout, q, grid, c->stream);
+        e = twocta ? PipeLaunch<NN>::k1q(c->noise != nullptr, potential != 0, mout, q, grid, c->stream)
+                   : PipeLaunch<NN>::k1p(c->noise != nullptr, potential != 0, mout, q, grid, c->stream);
         mark(c, 1);
       });
       c->launches++;

@@ -166,13 +166,27 @@ __host__ __device__ __forceinline__ philox_out philox4x32_10(uint32_t c0, uint32
 template <typename T>
 __device__ __forceinline__ cpx<T> box_muller(uint32_t wa, uint32_t wb);
 
+// MUFU wrappers with flush-to-zero semantics: a bare MUFU, without the denormal pre/post
+// scaling (FSETP + 2 predicated ops) the non-ftz forms carry.  Every argument on the hot path
+// is a normal number (u1 >= 2^-24, -2 ln u1 >= 1.19e-7, k^2 >= 5.9e-7 up to 4096^3 at 2 Mpc/h),
+// for which both forms return the same bits.
+__device__ __forceinline__ float lg2_ftz(float x) {
+  float r;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float sqrt_ftz(float x) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
 template <>
 __device__ __forceinline__ cpx<float> box_muller<float>(uint32_t wa, uint32_t wb) {
   float u1 = __int_as_float(0x3f800000u | (wa >> 9)) + (-1.0f + 5.9604644775390625e-8f);
-  float l2 = __log2f(u1);                                   // MUFU.LG2
+  float l2 = lg2_ftz(u1);                                   // MUFU.LG2
   float r2 = l2 * -1.3862943611198906f;                     // -2 ln2 * log2(u1) = -2 ln(u1)
-  float r;
-  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(r2));
+  float r = sqrt_ftz(r2);                                   // MUFU.SQRT
   float ang = (float)(int32_t)wb * 1.4629180792671596e-9f;  // pi / 2^31
   float s, c;
   __sincosf(ang, &s, &c);
@@ -286,7 +300,15 @@ __device__ __forceinline__ T sigma_eval(const SigmaTable<T>& tab, T ksq, int* bi
 __device__ __forceinline__ float sigma_hinge(const SigmaTable<float>& tab, float ksq) {
   const int c = min(max(coarse_cell(ksq, tab.shift) - tab.lut_base, 0), tab.lut_n - 1);
   const float4 h = __ldg(reinterpret_cast<const float4*>(tab.hinge) + c);
-  const float lg = __log2f(ksq);
+  const float lg = lg2_ftz(ksq);
+  return fmaf(h.w, fmaxf(lg - h.z, 0.f), fmaf(h.y, lg, h.x));
+}
+// same, with the cell table staged in shared memory and indexed without clamping: `hinge0`
+// points at the (virtual) entry of cell id 0, and the host's hinge_ok check guarantees that the
+// cell of every non-zero mode of the grid lies inside the table
+__device__ __forceinline__ float sigma_hinge_smem(const float4* hinge0, int shift, float ksq) {
+  const float4 h = hinge0[coarse_cell(ksq, shift)];
+  const float lg = lg2_ftz(ksq);
   return fmaf(h.w, fmaxf(lg - h.z, 0.f), fmaf(h.y, lg, h.x));
 }
 

@@ -28,6 +28,10 @@ struct PipeLaunch {
   // fused y + z pass (this N = ny); nz in 64..2048
   static int k23p(int nz, const CUtensorMap& in, const CUtensorMap& out, const pipe::K23Params& p, int grid,
                   cudaStream_t s);
+  // two-CTAs-per-SM variant of k1p; hinge_cells = entries of the sigma cell table staged in
+  // shared memory.  k1q_fits() says whether that table fits next to the work buffer.
+  static int k1q(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s);
+  static bool k1q_fits(int hinge_cells);
   static int tile_cols();   // TZ
   static int box_rows();    // rows per TMA box of the store map
 };

@@ -695,6 +695,144 @@ k1p_generate_xfft(const __grid_constant__ K1PMaps maps, const K1PParams p) {
 }
 
 // ----------------------------------------------------------------------------------------
+// k1q: the same pass as k1p laid out for TWO resident CTAs per SM (16 warps instead of 8).
+// k1p is issue-bound with two warps per scheduler and long dependent chains (Philox rounds,
+// MUFU); it reaches 60 % issue utilisation.  Here one CTA needs a single padded buffer
+// (66 KB) and at most 128 registers per thread:
+//   * step A writes the padded work buffer straight from registers (as in k1p);
+//   * step B is IN PLACE: every thread reads its R2-point sub-transform(s) out of the work
+//     buffer, all threads synchronise, and the results go back into the same memory in the
+//     dense [NX][TZ] layout the TMA store wants -- no separate store ring;
+//   * the step twiddles W_NX^(j*k1) come from a shared-memory copy of the table instead of
+//     62 registers; the sigma(k) cell table is staged in shared memory as well;
+//   * the buffer is only written again after the next tile's modes have been generated in
+//     registers (most of the tile time), so the TMA store read-out is hidden.
+// While one CTA of an SM generates (ALU/XU heavy) the other usually transforms (FMA heavy).
+// ----------------------------------------------------------------------------------------
+template <int NX>
+constexpr int k1q_smem_bytes(int hinge_cells) {
+  return SPlan<NX>::kWorkBytes + NX * 8 + hinge_cells * 16;
+}
+
+template <int NX, bool INJ, bool POT>
+__global__ void __launch_bounds__(kConsumers, 2)
+k1q_generate_xfft(const __grid_constant__ K1PMaps maps, const K1PParams p) {
+  using P = SPlan<NX>;
+  using L = LayoutStridedPad<P::TZ, P::M>;
+  constexpr int R1 = P::R1, R2 = P::R2, M = P::M, TZ = P::TZ;
+  static_assert(M * TZ == kConsumers, "one step-A item per thread");
+  static_assert(R1 % R2 == 0, "step B items per thread");
+  constexpr int IB = R1 / R2;          // step-B items per thread (R1*TZ items / 256 threads)
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  cpx<float>* const work = reinterpret_cast<cpx<float>*>(smem_raw);
+  cpx<float>* const tws = reinterpret_cast<cpx<float>*>(smem_raw + P::kWorkBytes);
+  float4* const hinge_s = reinterpret_cast<float4*>(smem_raw + P::kWorkBytes + NX * 8);
+  const int tid = threadIdx.x;
+  const int first = blockIdx.x, step = gridDim.x;
+  if (tid == 0) tma_prefetch_desc(&maps.m[0]);
+  for (int q = tid; q < NX; q += kConsumers) tws[q] = ldg_cpx(p.tw + q);
+  if constexpr (!INJ) {
+    for (int q = tid; q < p.tab.lut_n; q += kConsumers)
+      hinge_s[q] = __ldg(reinterpret_cast<const float4*>(p.tab.hinge) + q);
+  }
+  __syncthreads();
+  const float4* const hinge0 = hinge_s - p.tab.lut_base;   // entry of cell id 0 (never dereferenced)
+  const int shift = p.tab.shift;
+
+  const ModeGeom<float>& g = p.geom;
+  const int c = tid % TZ, j = tid / TZ;
+  const int nzh = g.nz / 2 + 1;
+  const float fj = (float)j;
+  const uint64_t dq = (uint64_t)M * g.ny * nzh;   // Philox counter step between m and m+1
+  cpx<float>* const wa = work + L::idx2(0, j, c);
+  for (int t = first; t < p.ntiles; t += step) {
+    const int iyl = t / p.ztiles, z0 = (t % p.ztiles) * TZ;
+    const int iy = p.y0 + iyl;
+    const int iz = z0 + c;
+    cpx<float> v[R1];
+    if (iz == 0) {
+      // packed column (iz=0 plane) + i*(iz=nz/2 plane): precomputed by gen_packed_plane_kernel
+      const cpx<float>* pp = p.plane + (size_t)j * p.ny_local + iyl;
+      sfor<0, R1>([&](auto mi) {
+        constexpr int m = decltype(mi)::value;
+        v[m] = ldg_cpx(pp + (size_t)(M * m) * p.ny_local);
+      });
+    } else if constexpr (INJ) {
+      sfor<0, R1>([&](auto mi) {
+        constexpr int m = decltype(mi)::value;
+        v[m] = raw_mode(g, p.tab, j + M * m, iy, iz);
+      });
+    } else {
+      const float ksq_yz = ksq_canon(0.f, mode_sq<float>(iy, g.ny), mode_sq<float>(iz, g.nz), g.k0x2,
+                                     g.k0y2, g.k0z2);
+      const uint64_t q0 = ((uint64_t)j * g.ny + iy) * nzh + iz;
+      sfor<0, R1 / 2>([&](auto mi) {
+        constexpr int m = decltype(mi)::value;
+        const float f1 = fj + (float)(M * m), f2 = f1 - (float)(NX / 2);
+        const float ks1 = __fmaf_rn(f1 * f1, g.k0x2, ksq_yz);
+        const float ks2 = __fmaf_rn(f2 * f2, g.k0x2, ksq_yz);
+        float s1 = sigma_hinge_smem(hinge0, shift, ks1), s2 = sigma_hinge_smem(hinge0, shift, ks2);
+        if constexpr (POT) {
+          s1 = __fdividef(s1, ks1);   // k^2 > 0 off the iz = 0 plane
+          s2 = __fdividef(s2, ks2);
+        }
+        const uint64_t q = q0 + (uint64_t)m * dq;
+        philox_out o = philox4x32_10((uint32_t)q, (uint32_t)(q >> 32), 0u, 0u, g.key0, g.key1);
+        cpx<float> n1 = box_muller<float>(o.w[0], o.w[1]);
+        cpx<float> n2 = box_muller<float>(o.w[2], o.w[3]);
+        v[m] = {s1 * n1.x, s1 * n1.y};
+        v[m + R1 / 2] = {s2 * n2.x, s2 * n2.y};
+      });
+    }
+    fft_dif<R1, true>(v);
+    // the previous tile's TMA store must have finished reading the buffer
+    if (tid == 0) bulk_wait_read0();
+    __syncthreads();
+    sfor<0, R1>([&](auto ki) {
+      constexpr int k1 = decltype(ki)::value;
+      cpx<float> x = v[brev<R1>(k1)];
+      if constexpr (k1 > 0) x = cmul(x, ld_cpx(tws + j * k1));
+      st_cpx(wa + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), x);
+    });
+    __syncthreads();
+    // step B in place: item w = tid + q*256 -> (k1, column) = (w / TZ, w % TZ)
+    cpx<float> u[IB][R2];
+    sfor<0, IB>([&](auto qi) {
+      constexpr int q = decltype(qi)::value;
+      const int w = tid + q * kConsumers;
+      const cpx<float>* wp = work + L::idx2(w / TZ, 0, w % TZ);
+      sfor<0, R2>([&](auto ji) {
+        constexpr int jj = decltype(ji)::value;
+        u[q][jj] = ld_cpx(wp + (L::idx2(0, jj, 0) - L::idx2(0, 0, 0)));
+      });
+    });
+    __syncthreads();
+    sfor<0, IB>([&](auto qi) {
+      constexpr int q = decltype(qi)::value;
+      const int w = tid + q * kConsumers;
+      const int k1 = w / TZ, cc = w % TZ;
+      fft_dif<R2, true>(u[q]);
+      sfor<0, R2>([&](auto ki) {
+        constexpr int k2 = decltype(ki)::value;
+        st_cpx(work + (k1 + R1 * k2) * TZ + cc, u[q][brev<R2>(k2)]);
+      });
+    });
+    fence_proxy_async();
+    __syncthreads();
+    if (tid == 0) {
+      // boxes never straddle two destinations (box rows = min(256, nxl), both powers of two)
+      const int box = p.nxl < P::kBoxRows ? p.nxl : P::kBoxRows;
+      for (int r0 = 0; r0 < NX; r0 += box) {
+        const int d = r0 / p.nxl;
+        tma_store_3d(&maps.m[d], work + r0 * TZ, 2 * z0, iyl, r0 - d * p.nxl);
+      }
+      bulk_commit();
+    }
+  }
+  if (tid == 0) bulk_wait0();
+}
+
+// ----------------------------------------------------------------------------------------
 // k23p: the y pass and the z (c2r) pass in ONE persistent kernel, so that the y-pass output of
 // an x-plane is still in L2 when the z pass reads it (the plane's tiles are visited a few
 // planes later, and the 126 MB L2 is write-back): DRAM sees 8 B/cell for both passes instead

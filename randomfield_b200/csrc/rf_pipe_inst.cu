@@ -52,6 +52,25 @@ int PipeLaunch<N>::k1p(bool injected, bool potential, const pipe::K1PMaps& out, 
   if (injected) return potential ? launch_k1p<true, true>(out, p, grid, s) : launch_k1p<true, false>(out, p, grid, s);
   return potential ? launch_k1p<false, true>(out, p, grid, s) : launch_k1p<false, false>(out, p, grid, s);
 }
+template <bool INJ, bool POT>
+static int launch_k1q(const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s) {
+  const int smem = pipe::k1q_smem_bytes<N>(INJ ? 0 : p.tab.lut_n);
+  int e;
+  if ((e = set_smem_pipe(pipe::k1q_generate_xfft<N, INJ, POT>, smem))) return e;
+  pipe::k1q_generate_xfft<N, INJ, POT><<<grid, pipe::kConsumers, smem, s>>>(out, p);
+  return (int)cudaGetLastError();
+}
+template <>
+int PipeLaunch<N>::k1q(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p,
+                       int grid, cudaStream_t s) {
+  if (injected) return potential ? launch_k1q<true, true>(out, p, grid, s) : launch_k1q<true, false>(out, p, grid, s);
+  return potential ? launch_k1q<false, true>(out, p, grid, s) : launch_k1q<false, false>(out, p, grid, s);
+}
+template <>
+bool PipeLaunch<N>::k1q_fits(int hinge_cells) {
+  // two CTAs (+1 KB reserved each) inside the 228 KB of an SM
+  return pipe::k1q_smem_bytes<N>(hinge_cells) <= 112 * 1024;
+}
 template <>
 int PipeLaunch<N>::tile_cols() {
   return pipe::SPlan<N>::TZ;

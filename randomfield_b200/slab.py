@@ -95,6 +95,7 @@ class SlabEngine(object):
     def generate(self, seed, potential=False, zscale=None, want_stats=True):
         """seed -> this rank's real-space x-slab, left resident on the device."""
         import torch
+        import torch.distributed as dist
         with torch.cuda.stream(self.stream):
             if self.world == 1:
                 self.engine.generate_delta(seed, potential, zscale, want_stats)

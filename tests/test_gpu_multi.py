@@ -67,13 +67,15 @@ def _ngpu():
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs two GPUs")
-def test_nccl_two_ranks_matches_single(tmp_path):
-    """Real one-process-per-GPU run: rank slabs written to disk, compared with world=1."""
+@pytest.mark.parametrize("direct", ["1", "0"])
+def test_nccl_two_ranks_matches_single(tmp_path, direct):
+    """Real one-process-per-GPU run (direct peer stores, and the NCCL all-to-all): rank slabs
+    written to disk, compared with world=1."""
     script = os.path.join(ROOT, "tests", "multi_worker.py")
     out = str(tmp_path)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
-           "--master-addr", "127.0.0.1", "--master-port", "29533", script, out]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+           "--master-addr", "127.0.0.1", "--master-port", "29533" if direct == "1" else "29535", script, out]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, RF_DIRECT=direct))
     assert r.returncode == 0, r.stdout + r.stderr
     from randomfield_b200 import slab
     ref, _, std1 = slab.run_virtual_slabs(128, 128, 64, 2.0, oracle.load_default_power(), seed=42, world=1)
