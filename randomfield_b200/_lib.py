@@ -11,7 +11,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librf_b200.so")
+# RF_LIB: load another build of the same library (A/B timing of compile-time variants)
+LIB_PATH = os.environ.get("RF_LIB") or os.path.join(_HERE, "librf_b200.so")
 
 RF_F32, RF_F64 = 0, 1
 RF_BUF_FIELD, RF_BUF_RECV, RF_BUF_PARTIALS = 0, 1, 2

@@ -589,7 +589,16 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
   c->field_is_real = false;
   c->stats_valid = false;
   if constexpr (std::is_same<T, float>::value) {
-    if (c->pipe && c->nx <= 1024 && c->hinge_ok) {
+    bool k1_pipe = c->pipe && c->nx <= 4096 && c->hinge_ok;
+    if (k1_pipe && c->nx > 1024) {
+      // rf_big.cuh kernels stage the sigma cell table in shared memory; 32-byte-wide tiles
+      // (nx = 4096) need nz/2 % 4 == 0, 64-byte ones nz/2 % 8 == 0 -- true for nz >= 64
+      if (c->nx == 2048) k1_pipe = PipeLaunch<2048>::k1p_fits(c->noise ? 0 : c->lut_n);
+      else k1_pipe = PipeLaunch<4096>::k1p_fits(c->noise ? 0 : c->lut_n);
+      const char* eb = getenv("RF_BIG");
+      if (eb && eb[0] == '0') k1_pipe = false;
+    }
+    if (k1_pipe) {
       pipe::K1PParams q;
       q.geom = g; q.tab = tab; q.tw = (const cpx<float>*)c->tw_x;
       q.ny_local = c->nyl; q.y0 = c->rank * c->nyl;
@@ -606,7 +615,7 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
       int e = 0;
       pipe::K1PMaps mout;
       memset(&mout, 0, sizeof(mout));
-      RF_DISPATCH_PIPE1K(c->nx, {
+      RF_DISPATCH_PIPE(c->nx, {
         const int tz = PipeLaunch<NN>::tile_cols();
         q.ztiles = nzc / tz;
         q.ntiles = c->nyl * q.ztiles;
@@ -629,7 +638,7 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
           if (e2) return e2;
         }
         const bool twocta = c->k1q && PipeLaunch<NN>::k1q_fits(c->lut_n);
-        int grid = std::min(q.ntiles, (twocta ? 2 : 1) * c->num_sms);
+        int grid = std::min(q.ntiles, (twocta ? 2 : PipeLaunch<NN>::ctas_per_sm()) * c->num_sms);
         mark(c, 0);
         e = twocta ? PipeLaunch<NN>::k1q(c->noise != nullptr, potential != 0, mout, q, grid, c->stream)
                    : PipeLaunch<NN>::k1p(c->noise != nullptr, potential != 0, mout, q, grid, c->stream);
@@ -727,12 +736,14 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
     int e = 0;
     bool done2 = false, fused_done = false;
     if constexpr (std::is_same<T, float>::value) {
-      if (c->pipe && c->ny <= 1024) {
+      const char* eb2 = getenv("RF_BIG");
+      if (c->pipe && (c->ny <= 1024 || (c->ny <= 4096 && !(eb2 && eb2[0] == '0')))) {
         pipe::K2PParams q;
         q.tw = (const cpx<float>*)c->tw_y;
         q.rows_per_src = p2.rows_per_src;
+        q.out = (cpx<float>*)p2.out; q.out_outer = p2.out_outer; q.out_row = p2.out_row;
         CUtensorMap min, mout;
-        RF_DISPATCH_PIPE1K(c->ny, {
+        RF_DISPATCH_PIPE(c->ny, {
           const int tz = PipeLaunch<NN>::tile_cols();
           q.ztiles = nzc / tz;
           q.ntiles = c->nxl * q.ztiles;
@@ -750,7 +761,7 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
           e2 = make_tensor_map(&mout, (void*)p2.out, 3, dout, sout, bout);
           if (e2) return e2;
           q.tile0 = 0;
-          int grid = std::min(q.ntiles, c->num_sms);
+          int grid = std::min(q.ntiles, PipeLaunch<NN>::ctas_per_sm() * c->num_sms);
           const int t3_per_plane = (int)((long long)c->ny * (c->nz / 2) * 8 / pipe::kTileBytes);
           if (c->fuse && t3_per_plane >= 1) {
             // y and z passes in one persistent kernel (z pass reads the y-pass output from L2)
@@ -780,7 +791,7 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
               f.k3.partials = c->partials;
             }
             mark(c, 2);
-            e = PipeLaunch<NN>::k23p(c->nz, min, mout, f, grid, c->stream);
+            if constexpr (NN <= 1024) e = PipeLaunch<NN>::k23p(c->nz, min, mout, f, grid, c->stream);
             mark(c, 3);
             mark(c, 4);
             mark(c, 5);

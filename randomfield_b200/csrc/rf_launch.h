@@ -4,6 +4,7 @@
 #pragma once
 #include "rf_fast.cuh"
 #include "rf_pipe.cuh"
+#include "rf_big.cuh"
 
 namespace rf {
 
@@ -21,7 +22,7 @@ template <int N>
 struct PipeLaunch {
   static int k3p(const pipe::K3PParams& p, int grid, cudaStream_t s);
   static int k3p_lines_per_tile();
-  // N <= 1024 only
+  // N <= 1024: rf_pipe.cuh kernels; N = 2048, 4096: the single-buffer kernels of rf_big.cuh
   static int k2p(const CUtensorMap& in, const CUtensorMap& out, const pipe::K2PParams& p, int grid,
                  cudaStream_t s);
   static int k1p(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s);
@@ -32,6 +33,8 @@ struct PipeLaunch {
   // shared memory.  k1q_fits() says whether that table fits next to the work buffer.
   static int k1q(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s);
   static bool k1q_fits(int hinge_cells);
+  static bool k1p_fits(int hinge_cells);   // false: the sigma cell table does not fit (rf_big.cuh kernels)
+  static int ctas_per_sm();  // resident CTAs per SM of k2p / k1p (grid = this * SM count)
   static int tile_cols();   // TZ
   static int box_rows();    // rows per TMA box of the store map
 };

@@ -493,6 +493,10 @@ struct K2PParams {
   int ztiles;              // ncols / TZ
   int rows_per_src;        // rows of a line held by one source block (N when single GPU)
   int box_rows;            // rows per TMA box = min(256, rows_per_src)
+  // output addressing for kernels that store from registers (rf_big.cuh): element
+  // out[outer * out_outer + row * out_row + column]
+  cpx<float>* out;
+  long long out_outer, out_row;
 };
 
 template <int N>
@@ -730,7 +734,8 @@ k1q_generate_xfft(const __grid_constant__ K1PMaps maps, const K1PParams p) {
   const int tid = threadIdx.x;
   const int first = blockIdx.x, step = gridDim.x;
   if (tid == 0) tma_prefetch_desc(&maps.m[0]);
-  for (int q = tid; q < NX; q += kConsumers) tws[q] = ldg_cpx(p.tw + q);
+  // tws[k1 * M + j] = W_NX^(j * k1): the lanes of a warp (consecutive j) read consecutive words
+  for (int q = tid; q < NX; q += kConsumers) tws[q] = ldg_cpx(p.tw + (q % M) * (q / M));
   if constexpr (!INJ) {
     for (int q = tid; q < p.tab.lut_n; q += kConsumers)
       hinge_s[q] = __ldg(reinterpret_cast<const float4*>(p.tab.hinge) + q);
@@ -791,7 +796,7 @@ k1q_generate_xfft(const __grid_constant__ K1PMaps maps, const K1PParams p) {
     sfor<0, R1>([&](auto ki) {
       constexpr int k1 = decltype(ki)::value;
       cpx<float> x = v[brev<R1>(k1)];
-      if constexpr (k1 > 0) x = cmul(x, ld_cpx(tws + j * k1));
+      if constexpr (k1 > 0) x = cmul(x, ld_cpx(tws + k1 * M + j));
       st_cpx(wa + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), x);
     });
     __syncthreads();

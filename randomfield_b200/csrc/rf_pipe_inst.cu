@@ -1,5 +1,5 @@
 // rf_pipe_inst.cu -- one instantiation unit of the TMA-pipelined kernels: compile with
-//   -DRF_PIPE_N=<power of two in [64, 2048]>
+//   -DRF_PIPE_N=<power of two in [64, 4096]>
 #include "rf_launch.h"
 
 #ifndef RF_PIPE_N
@@ -78,6 +78,66 @@ int PipeLaunch<N>::tile_cols() {
 template <>
 int PipeLaunch<N>::box_rows() {
   return pipe::SPlan<N>::kBoxRows;
+}
+template <>
+bool PipeLaunch<N>::k1p_fits(int) {
+  return true;
+}
+template <>
+int PipeLaunch<N>::ctas_per_sm() {
+  return 1;
+}
+#else
+// ---- axes of 2048 / 4096 points: single-buffer in-place kernels of rf_big.cuh ----
+template <>
+int PipeLaunch<N>::k2p(const CUtensorMap& in, const CUtensorMap& out, const pipe::K2PParams& p, int grid,
+                       cudaStream_t s) {
+  constexpr int smem = big::k2b_smem_bytes<N>();
+  static_assert(smem <= 227 * 1024, "k2b shared memory");
+  int e;
+  if ((e = set_smem_pipe(big::k2b_strided_fft<N>, smem))) return e;
+  (void)out;   // results are stored from registers
+  big::k2b_strided_fft<N><<<grid, big::BPlan<N>::NT, smem, s>>>(in, p);
+  return (int)cudaGetLastError();
+}
+template <bool INJ, bool POT>
+static int launch_k1b(const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s) {
+  const int smem = big::kb_smem_bytes<N>(INJ ? 0 : p.tab.lut_n * 16);
+  int e;
+  if ((e = set_smem_pipe(big::k1b_generate_xfft<N, INJ, POT>, smem))) return e;
+  big::k1b_generate_xfft<N, INJ, POT><<<grid, big::BPlan<N>::NT, smem, s>>>(out, p);
+  return (int)cudaGetLastError();
+}
+template <>
+int PipeLaunch<N>::k1p(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p,
+                       int grid, cudaStream_t s) {
+  if (injected) return potential ? launch_k1b<true, true>(out, p, grid, s) : launch_k1b<true, false>(out, p, grid, s);
+  return potential ? launch_k1b<false, true>(out, p, grid, s) : launch_k1b<false, false>(out, p, grid, s);
+}
+template <>
+int PipeLaunch<N>::k1q(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p,
+                       int grid, cudaStream_t s) {
+  return k1p(injected, potential, out, p, grid, s);
+}
+template <>
+bool PipeLaunch<N>::k1q_fits(int) {
+  return false;
+}
+template <>
+bool PipeLaunch<N>::k1p_fits(int hinge_cells) {
+  return big::kb_smem_bytes<N>(hinge_cells * 16) <= (big::BPlan<N>::CTAS == 2 ? 112 : 226) * 1024;
+}
+template <>
+int PipeLaunch<N>::ctas_per_sm() {
+  return big::BPlan<N>::CTAS;
+}
+template <>
+int PipeLaunch<N>::tile_cols() {
+  return big::BPlan<N>::TZ;
+}
+template <>
+int PipeLaunch<N>::box_rows() {
+  return big::BGeom<N>::kBoxRows;
 }
 #endif
 

@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("shape", [(64, 64, 64), (128, 256, 64), (256, 128, 128)])
+@pytest.mark.parametrize("shape", [(64, 64, 64), (128, 256, 64), (256, 128, 128), (4096, 64, 64), (64, 2048, 64)])
 def test_field_bit_identical_across_decompositions(shape):
     from randomfield_b200 import slab
     power = oracle.load_default_power()
@@ -27,7 +27,7 @@ def test_field_bit_identical_across_decompositions(shape):
         assert abs(std - std1) <= 1e-9 * std1
 
 
-@pytest.mark.parametrize("shape", [(64, 64, 64), (256, 128, 128)])
+@pytest.mark.parametrize("shape", [(64, 64, 64), (256, 128, 128), (2048, 128, 64), (128, 4096, 64)])
 def test_direct_exchange_bit_identical(shape):
     """Pass 1 storing straight into the receive buffers of the owning ranks (peer memory; here
     all ranks live on one GPU) gives the same bits as the all-to-all path."""

@@ -143,6 +143,8 @@ def test_injected_noise_matches_golden(lib, golden_dir, name):
 # ------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("shape,dtype", [((64, 64, 64), np.float32), ((64, 128, 256), np.float32),
                                          ((64, 64, 2048), np.float32), ((64, 64, 4096), np.float32),
+                                         ((2048, 64, 64), np.float32), ((64, 2048, 64), np.float32),
+                                         ((4096, 64, 64), np.float32), ((64, 4096, 128), np.float32),
                                          ((64, 64, 64), np.float64), ((12, 10, 8), np.float32)])
 def test_philox_field_matches_oracle(lib, shape, dtype):
     spacing, seed = 2.0, 2024
