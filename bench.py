@@ -40,6 +40,18 @@ PASS_NAMES = ("k1_generate_xfft", "k2_strided_fft", "k3_c2r_lines")
 PIPE_NAMES = ("k1p_generate_xfft", "k2p_strided_fft", "k3p_c2r_lines")
 
 
+def kernel_names(grid, pipelined):
+    """Names of the three pass kernels the library launches for this grid (rf_api.cu dispatch)."""
+    if not pipelined:
+        return PASS_NAMES
+    k1q = os.environ.get("RF_K1Q", "1") != "0"
+    big = os.environ.get("RF_BIG", "1") != "0"
+    k1 = ("k1q_generate_xfft" if k1q else "k1p_generate_xfft") if grid[0] <= 1024 else (
+        "k1b_generate_xfft" if big else PASS_NAMES[0])
+    k2 = "k2p_strided_fft" if grid[1] <= 1024 else ("k2b_strided_fft" if big else PASS_NAMES[1])
+    return (k1, k2, "k3p_c2r_lines")
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -249,7 +261,7 @@ def run_ours(args):
 
     peak, peak_src = measured_peaks()
     local_cells = cells / world
-    names = PIPE_NAMES if pipelined else PASS_NAMES
+    names = kernel_names(grid, pipelined)
     dom = int(np.argmax(pass_ms))
     traffic = None
     try:   # DRAM bytes per launch from the committed ncu --set full capture of the same workload

@@ -254,7 +254,7 @@ extern "C" int rf_set_direct(rf_ctx* c, int enabled) {
 
 extern "C" int rf_is_fast(rf_ctx* c) { return c && c->fast ? 1 : 0; }
 extern "C" int rf_is_pipelined(rf_ctx* c) {
-  return c && c->pipe && c->nx <= 1024 && c->ny <= 1024 && c->nz <= 2048 ? 1 : 0;
+  return c && c->pipe && c->nx <= 4096 && c->ny <= 4096 && c->nz <= 4096 ? 1 : 0;
 }
 extern "C" long long rf_launch_count(rf_ctx* c) { return c ? c->launches : 0; }
 extern "C" long long rf_field_elems(rf_ctx* c) {
