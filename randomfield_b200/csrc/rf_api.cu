@@ -42,6 +42,11 @@ struct rf_ctx {
   bool pipe = false;        // TMA-pipelined kernels (f32, env RF_PIPE != 0)
   bool fuse = false;        // fused y+z kernel k23p (env RF_FUSE != 0)
   bool k1q = true;          // pass 1 with two CTAs per SM (env RF_K1Q=0: one-CTA k1p)
+  bool fuse12 = false;      // passes 1 + 2 in one kernel when nx == ny in {512, 1024}, single GPU (env RF_FUSE12=1)
+  bool pass2_done = false;  // set by the fused kernel: rf_finish_yz starts at pass 3
+  int hinge_lo = 0, hinge_hi = -1;   // cells of the sigma table the grid's modes can touch
+  unsigned int* zt_done = nullptr;  // [sched_n] per-z-tile counters of the fused pass 1 + 2 kernel
+  int sched_n = 0;
   unsigned int* sched = nullptr;   // [1 + nxl] ticket + per-plane counters of k23p
   void* peer_recv[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   bool direct = false;      // pass 1 stores straight into the peers' receive buffers
@@ -129,6 +134,9 @@ extern "C" int rf_create(int nx, int ny, int nz, int dtype, int rank, int world,
     c->fuse = c->pipe && ny <= 1024 && nz <= 2048 && envf && envf[0] == '1';
     const char* envq = getenv("RF_K1Q");
     c->k1q = !(envq && envq[0] == '0');
+    // opt-in: measured slower than k1q + k2p on B200
+    const char* env12 = getenv("RF_FUSE12");
+    c->fuse12 = env12 && env12[0] == '1';
   }
   RF_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
   c->stream = c->own_stream;
@@ -162,7 +170,7 @@ extern "C" int rf_destroy(rf_ctx* c) {
   if (!c) return RF_OK;
   cudaStreamSynchronize(c->stream);
   void* ptrs[] = {c->field, c->recv, c->partials, c->stats_dev, c->tw_x, c->tw_y, c->tw_z,
-                  c->tw_zh, c->knots, c->cells, c->hinge, c->plane, c->sched, c->noise, c->zs_dev, c->da_dev, c->db_dev};
+                  c->tw_zh, c->knots, c->cells, c->hinge, c->plane, c->sched, c->zt_done, c->noise, c->zs_dev, c->da_dev, c->db_dev};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -402,6 +410,8 @@ static int build_table(rf_ctx* c, int n, const double* k, const double* sigma) {
     const int elo = cell_of((T)kmin2, shift) - base - 1, ehi = cell_of((T)kmax2, shift) - base + 1;
     hinge_ok = elo >= 1 && ehi <= ln - 2;
     for (int e = std::max(elo, 1); hinge_ok && e <= ehi; ++e) hinge_ok = valid[e] != 0;
+    c->hinge_lo = std::max(elo, 0);
+    c->hinge_hi = std::min(ehi, ln - 1);
   }
   if (c->knots) cudaFree(c->knots);
   if (c->cells) cudaFree(c->cells);
@@ -546,6 +556,13 @@ static int ensure_partials(rf_ctx* c, long long n) {
     default: return fail(RF_ERR_ARG, "size not compiled");\
   }
 
+#define RF_DISPATCH_FUSE12(N_, ...)                     \
+  switch (N_) {                                         \
+    case 512: { constexpr int NN = 512; __VA_ARGS__; } break;  \
+    case 1024: { constexpr int NN = 1024; __VA_ARGS__; } break;\
+    default: return fail(RF_ERR_ARG, "size not compiled");\
+  }
+
 #define RF_DISPATCH_N(N_, ...)                          \
   switch (N_) {                                         \
     case 64: { constexpr int NN = 64; __VA_ARGS__; } break;    \
@@ -588,6 +605,7 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
   SigmaTable<T> tab = make_tab<T>(c);
   c->field_is_real = false;
   c->stats_valid = false;
+  c->pass2_done = false;
   if constexpr (std::is_same<T, float>::value) {
     bool k1_pipe = c->pipe && c->nx <= 4096 && c->hinge_ok;
     if (k1_pipe && c->nx > 1024) {
@@ -615,6 +633,68 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
       int e = 0;
       pipe::K1PMaps mout;
       memset(&mout, 0, sizeof(mout));
+      c->pass2_done = false;
+      if (c->fuse12 && c->world == 1 && !c->direct && c->nx == c->ny && (c->nx == 512 || c->nx == 1024) &&
+          !c->noise && c->hinge_hi >= c->hinge_lo) {
+        bool launched = false;
+        RF_DISPATCH_FUSE12(c->nx, {
+          const int cells = c->hinge_hi - c->hinge_lo + 1;
+          if (PipeLaunch<NN>::k12_fits(cells)) {
+            const int tz = PipeLaunch<NN>::tile_cols();
+            q.ztiles = nzc / tz;
+            q.ntiles = c->ny * q.ztiles;
+            q.nxl = c->nx;
+            fuse12::K12Params f;
+            f.k1 = q;
+            f.tw_y = (const cpx<float>*)c->tw_y;
+            f.nplanes = c->nx;
+            f.hinge_first = c->hinge_lo;
+            f.hinge_cells = cells;
+            f.out = (cpx<float>*)c->field;
+            f.out_outer = (long long)c->ny * nzc;
+            f.out_row = nzc;
+            f.zc = 8;
+            if (const char* ez = getenv("RF_ZC")) f.zc = std::max(1, atoi(ez));
+            while (f.zc > 1 && (q.ztiles % f.zc)) f.zc >>= 1;
+            if (c->sched_n < q.ztiles) {
+              if (c->zt_done) cudaFree(c->zt_done);
+              c->zt_done = nullptr;
+              RF_CUDA(cudaMalloc((void**)&c->zt_done, sizeof(unsigned int) * q.ztiles));
+              c->sched_n = q.ztiles;
+            }
+            f.dbg = 0;
+            if (const char* ed = getenv("RF_K12_DBG")) f.dbg = atoi(ed);
+            RF_CUDA(cudaMemsetAsync(c->zt_done, (f.dbg & 2) ? 0x7f : 0, sizeof(unsigned int) * q.ztiles, c->stream));
+            f.zt_done = c->zt_done;
+            // pass-1 store map (z, y, x), pass-2 load map (z, y rows, x plane, 1), store map (z, y, x plane)
+            uint64_t d1[3] = {(uint64_t)2 * nzc, (uint64_t)c->ny, (uint64_t)c->nx};
+            uint64_t s1[2] = {(uint64_t)nzc * 8, (uint64_t)c->ny * nzc * 8};
+            uint32_t b1[3] = {(uint32_t)2 * tz, 1, (uint32_t)PipeLaunch<NN>::box_rows()};
+            int e2 = make_tensor_map(&mout.m[0], c->field, 3, d1, s1, b1);
+            if (e2) return e2;
+            CUtensorMap min2, mout2;
+            uint64_t d2[4] = {(uint64_t)2 * nzc, (uint64_t)c->ny, (uint64_t)c->nx, 1};
+            uint64_t s2[3] = {(uint64_t)nzc * 8, (uint64_t)c->ny * nzc * 8, (uint64_t)c->nx * c->ny * nzc * 8};
+            uint32_t b2[4] = {(uint32_t)2 * tz, (uint32_t)PipeLaunch<NN>::box_rows(), 1, 1};
+            e2 = make_tensor_map(&min2, c->field, 4, d2, s2, b2);
+            if (e2) return e2;
+            uint32_t b3[3] = {(uint32_t)2 * tz, (uint32_t)PipeLaunch<NN>::box_rows(), 1};
+            e2 = make_tensor_map(&mout2, c->field, 3, d1, s1, b3);
+            if (e2) return e2;
+            const int grid = std::min(q.ntiles, c->num_sms);
+            mark(c, 0);
+            e = PipeLaunch<NN>::k12(potential != 0, mout, min2, mout2, f, grid, c->stream);
+            mark(c, 1);
+            launched = true;
+          }
+        });
+        if (launched) {
+          c->launches++;
+          RF_CUDA(e);
+          c->pass2_done = true;
+          return RF_OK;
+        }
+      }
       RF_DISPATCH_PIPE(c->nx, {
         const int tz = PipeLaunch<NN>::tile_cols();
         q.ztiles = nzc / tz;
@@ -735,9 +815,16 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
     }
     int e = 0;
     bool done2 = false, fused_done = false;
+    if (c->pass2_done) {
+      // pass 2 already ran inside the fused pass-1 + pass-2 kernel
+      c->pass2_done = false;
+      done2 = true;
+      mark(c, 2);
+      mark(c, 3);
+    }
     if constexpr (std::is_same<T, float>::value) {
       const char* eb2 = getenv("RF_BIG");
-      if (c->pipe && (c->ny <= 1024 || (c->ny <= 4096 && !(eb2 && eb2[0] == '0')))) {
+      if (!done2 && c->pipe && (c->ny <= 1024 || (c->ny <= 4096 && !(eb2 && eb2[0] == '0')))) {
         pipe::K2PParams q;
         q.tw = (const cpx<float>*)c->tw_y;
         q.rows_per_src = p2.rows_per_src;

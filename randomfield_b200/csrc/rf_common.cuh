@@ -31,8 +31,15 @@ template <typename T>
 __host__ __device__ __forceinline__ cpx<T> operator-(cpx<T> a, cpx<T> b) {
   return {a.x - b.x, a.y - b.y};
 }
+// The float form pins which product is fused into the FMA: left to the compiler the choice
+// differs from kernel to kernel, and the field must be bit-identical whichever kernels
+// (fused or separate passes, one GPU or several) produce it.
 template <typename T>
 __host__ __device__ __forceinline__ cpx<T> cmul(cpx<T> a, cpx<T> b) {
+#ifdef __CUDA_ARCH__
+  if constexpr (sizeof(T) == 4)
+    return {__fmaf_rn(a.x, b.x, -__fmul_rn(a.y, b.y)), __fmaf_rn(a.x, b.y, __fmul_rn(a.y, b.x))};
+#endif
   return {a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x};
 }
 template <typename T>
@@ -97,7 +104,10 @@ __device__ __forceinline__ cpx<T> mul_tw32(cpx<T> d) {
   } else {
     constexpr T c = (T)rf_cos32(k);
     constexpr T s = (T)(INV ? rf_sin32(k) : -rf_sin32(k));
-    return {d.x * c - d.y * s, d.x * s + d.y * c};
+    if constexpr (sizeof(T) == 4)
+      return {__fmaf_rn(d.x, c, -__fmul_rn(d.y, s)), __fmaf_rn(d.x, s, __fmul_rn(d.y, c))};
+    else
+      return {d.x * c - d.y * s, d.x * s + d.y * c};
   }
 }
 

@@ -5,6 +5,7 @@
 #include "rf_fast.cuh"
 #include "rf_pipe.cuh"
 #include "rf_big.cuh"
+#include "rf_fuse12.cuh"
 
 namespace rf {
 
@@ -34,6 +35,10 @@ struct PipeLaunch {
   static int k1q(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s);
   static bool k1q_fits(int hinge_cells);
   static bool k1p_fits(int hinge_cells);   // false: the sigma cell table does not fit (rf_big.cuh kernels)
+  // fused pass 1 + pass 2 (rf_fuse12.cuh; nx == ny == N <= 1024, single GPU, Philox path)
+  static int k12(bool potential, const pipe::K1PMaps& maps, const CUtensorMap& in, const CUtensorMap& out,
+                 const fuse12::K12Params& p, int grid, cudaStream_t s);
+  static bool k12_fits(int hinge_cells);
   static int ctas_per_sm();  // resident CTAs per SM of k2p / k1p (grid = this * SM count)
   static int tile_cols();   // TZ
   static int box_rows();    // rows per TMA box of the store map

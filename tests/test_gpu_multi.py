@@ -61,6 +61,23 @@ def test_potential_and_zscale_across_decompositions():
     assert np.array_equal(got, ref)
 
 
+def test_fused_pass12_kernel_bit_identical(monkeypatch):
+    """The opt-in fused pass-1 + pass-2 kernel (RF_FUSE12=1, rf_fuse12.cuh) gives the same bits as
+    the separate kernels."""
+    from randomfield_b200 import slab
+    power = oracle.load_default_power()
+    shape = (512, 512, 64)
+    monkeypatch.setenv("RF_FUSE12", "0")
+    ref, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1)
+    monkeypatch.setenv("RF_FUSE12", "1")
+    got, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1)
+    assert np.array_equal(got, ref)
+    gotp, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1, potential=True)
+    monkeypatch.setenv("RF_FUSE12", "0")
+    refp, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1, potential=True)
+    assert np.array_equal(gotp, refp)
+
+
 def _ngpu():
     import torch
     return torch.cuda.device_count()
