@@ -280,9 +280,11 @@ def run_ours(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(grid, world), "grid": list(grid),
                    "l2": "working set %.1f GB per GPU >> 126 MB L2, no flush needed" % (4 * local_cells / 1e9),
-                   "parallelism": ("y-slab k-space -> %s -> x-slab real space" % (
-                       "pass-1 stores into peer receive buffers over NVLink (no separate all-to-all)"
-                       if eng.direct else "NCCL all-to-all")) if world > 1 else "single GPU",
+                   "parallelism": ("y-slab k-space -> %s -> x-slab real space" % {
+                       "direct": "pass-1 stores into peer receive buffers over NVLink (no separate all-to-all)",
+                       "chunked": "copy-engine pushes into peer receive buffers, pipelined with passes 1 and 2 "
+                                  "over %d chunks of z columns" % eng.nchunks,
+                       "nccl": "NCCL all-to-all"}.get(eng.mode, eng.mode)) if world > 1 else "single GPU",
                    "field_std": std, "field_mean": mean},
         "roofline": {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,

@@ -141,6 +141,27 @@ int rf_ipc_close(void* ptr);
 int rf_set_peer_recv(rf_ctx* ctx, int rank, void* recv_ptr);
 int rf_set_direct(rf_ctx* ctx, int enabled);
 
+/* Chunked exchange (slab decomposition): the packed z columns (nz/2) are cut into `nchunks`
+ * chunks.  Pass 1 of chunk c writes a contiguous send block, the copy engines push its G
+ * blocks into the peers' receive buffers (rf_set_peer_recv pointers) on the context's comm
+ * stream while pass 1 of chunk c+1 and pass 2 of chunk c-1 run on the SMs -- the overlapped
+ * form of the global transpose of transform.Plan.execute (transform.py:303-315) when the
+ * field is slab-decomposed.  Call order per step (every rank):
+ *   rf_chunk_begin_step; [cross-rank fence on rf_comm_stream]
+ *   for c: rf_chunk_xpass(c); rf_chunk_exchange(c); [fence on rf_comm_stream]; rf_chunk_arrived(c);
+ *          rf_chunk_pass2(c-1)            (pass 2 of a chunk may be queued any time after arrived)
+ *   rf_chunk_pass2(last); rf_finish_yz    (pass 3 only)
+ * The fences (any cross-rank barrier ordered on the comm stream, e.g. a 1-element NCCL
+ * all-reduce) are the caller's: the library has no inter-process transport of its own.
+ * world == 1 runs the same kernels without copies (used by the tests). */
+int rf_chunk_config(rf_ctx* ctx, int nchunks);          /* 0: off, frees the send buffer */
+void* rf_comm_stream(rf_ctx* ctx);
+int rf_chunk_begin_step(rf_ctx* ctx);
+int rf_chunk_xpass(rf_ctx* ctx, uint64_t seed, int potential, int chunk);
+int rf_chunk_exchange(rf_ctx* ctx, int chunk);
+int rf_chunk_arrived(rf_ctx* ctx, int chunk);
+int rf_chunk_pass2(rf_ctx* ctx, int chunk);
+
 /* raw device pointers for zero-copy wrapping (torch / DLPack) and for the all-to-all */
 void* rf_device_ptr(rf_ctx* ctx, int which);
 long long rf_buffer_bytes(rf_ctx* ctx, int which);

@@ -55,6 +55,13 @@ SIGNATURES = {
     "rf_ipc_close": (_c.c_int, [_P]),
     "rf_set_peer_recv": (_c.c_int, [_P, _c.c_int, _P]),
     "rf_set_direct": (_c.c_int, [_P, _c.c_int]),
+    "rf_chunk_config": (_c.c_int, [_P, _c.c_int]),
+    "rf_comm_stream": (_c.c_void_p, [_P]),
+    "rf_chunk_begin_step": (_c.c_int, [_P]),
+    "rf_chunk_xpass": (_c.c_int, [_P, _c.c_uint64, _c.c_int, _c.c_int]),
+    "rf_chunk_exchange": (_c.c_int, [_P, _c.c_int]),
+    "rf_chunk_arrived": (_c.c_int, [_P, _c.c_int]),
+    "rf_chunk_pass2": (_c.c_int, [_P, _c.c_int]),
     "rf_is_fast": (_c.c_int, [_P]),
     "rf_is_pipelined": (_c.c_int, [_P]),
     "rf_launch_count": (_c.c_longlong, [_P]),
@@ -253,6 +260,29 @@ class Engine:
 
     def set_direct(self, enabled=True):
         check(lib().rf_set_direct(self._ctx, int(bool(enabled))))
+
+    # ---- chunked exchange (include/rf_b200.h: rf_chunk_*) ----
+    def chunk_config(self, nchunks):
+        check(lib().rf_chunk_config(self._ctx, int(nchunks)))
+
+    @property
+    def comm_stream(self):
+        return int(lib().rf_comm_stream(self._ctx) or 0)
+
+    def chunk_begin_step(self):
+        check(lib().rf_chunk_begin_step(self._ctx))
+
+    def chunk_xpass(self, seed, potential, chunk):
+        check(lib().rf_chunk_xpass(self._ctx, int(seed) & 0xFFFFFFFFFFFFFFFF, int(bool(potential)), int(chunk)))
+
+    def chunk_exchange(self, chunk):
+        check(lib().rf_chunk_exchange(self._ctx, int(chunk)))
+
+    def chunk_arrived(self, chunk):
+        check(lib().rf_chunk_arrived(self._ctx, int(chunk)))
+
+    def chunk_pass2(self, chunk):
+        check(lib().rf_chunk_pass2(self._ctx, int(chunk)))
 
     @property
     def is_fast(self):

@@ -50,6 +50,17 @@ struct rf_ctx {
   unsigned int* sched = nullptr;   // [1 + nxl] ticket + per-plane counters of k23p
   void* peer_recv[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   bool direct = false;      // pass 1 stores straight into the peers' receive buffers
+  // chunked exchange (rf_chunk_*): the packed z columns are cut into ck_n chunks; pass 1 of chunk
+  // c writes send[c] = [nx][nyl][wc], copy engines push its G blocks into the peers' recv[c] =
+  // [G][nxl][nyl][wc] while pass 1 of chunk c+1 and pass 2 of chunk c-1 run on the SMs
+  int ck_n = 0;             // chunks (0: off)
+  int ck_cur = -1;          // chunk the next pass-1 / pass-2 launch works on (-1: whole field)
+  void* send = nullptr;     // [ck_n][nx][nyl][wc]
+  cudaStream_t comm = nullptr;
+  cudaEvent_t ev_k1 = nullptr, ev_x = nullptr, ev_s = nullptr;
+  std::vector<cudaEvent_t> ev_xc;   // per chunk: exchange complete (recorded on the comm stream)
+  std::vector<cudaEvent_t> ck_ev;   // timing: [pass 1 | pass 2][chunk][start, stop]
+  bool last_chunked = false;        // the last step ran through rf_chunk_*
   int num_sms = 148;
   size_t esize = 4;         // sizeof(T)
   cudaStream_t own_stream = nullptr, stream = nullptr;
@@ -173,6 +184,12 @@ extern "C" int rf_destroy(rf_ctx* c) {
                   c->tw_zh, c->knots, c->cells, c->hinge, c->plane, c->sched, c->zt_done, c->noise, c->zs_dev, c->da_dev, c->db_dev};
   for (void* p : ptrs)
     if (p) cudaFree(p);
+  if (c->send) cudaFree(c->send);
+  for (cudaEvent_t ev : c->ck_ev) cudaEventDestroy(ev);
+  for (cudaEvent_t ev : c->ev_xc) cudaEventDestroy(ev);
+  if (c->comm) cudaStreamDestroy(c->comm);
+  for (cudaEvent_t e : {c->ev_k1, c->ev_x, c->ev_s})
+    if (e) cudaEventDestroy(e);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   delete c;
   return RF_OK;
@@ -211,7 +228,18 @@ extern "C" int rf_get_timing(rf_ctx* c, double* a, double* b, double* d) {
   if (!c || !c->timing || !c->fast) return fail(RF_ERR_STATE, "rf_get_timing: timing is off or generic path");
   RF_CUDA(cudaStreamSynchronize(c->stream));
   float t[3] = {0, 0, 0};
-  for (int i = 0; i < 3; ++i) RF_CUDA(cudaEventElapsedTime(&t[i], c->ev[2 * i], c->ev[2 * i + 1]));
+  if (c->last_chunked && (int)c->ck_ev.size() == 4 * c->ck_n) {
+    // chunked step: passes 1 and 2 are interleaved; report the sum of their chunk launches
+    for (int ps = 0; ps < 2; ++ps)
+      for (int k = 0; k < c->ck_n; ++k) {
+        float dt = 0;
+        RF_CUDA(cudaEventElapsedTime(&dt, c->ck_ev[(ps * c->ck_n + k) * 2], c->ck_ev[(ps * c->ck_n + k) * 2 + 1]));
+        t[ps] += dt;
+      }
+    RF_CUDA(cudaEventElapsedTime(&t[2], c->ev[4], c->ev[5]));
+  } else {
+    for (int i = 0; i < 3; ++i) RF_CUDA(cudaEventElapsedTime(&t[i], c->ev[2 * i], c->ev[2 * i + 1]));
+  }
   if (a) *a = t[0];
   if (b) *b = t[1];
   if (d) *d = t[2];
@@ -622,7 +650,7 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
       q.ny_local = c->nyl; q.y0 = c->rank * c->nyl;
       const int nzc = c->nz / 2;
       if (!c->plane) RF_CUDA(cudaMalloc(&c->plane, sizeof(cpx<float>) * (size_t)c->nx * c->nyl));
-      {
+      if (c->ck_cur <= 0) {
         const int total = c->nx * c->nyl;
         gen_packed_plane_kernel<float><<<std::min((total + 127) / 128, 148 * 16), 128, 0, c->stream>>>(
             g, tab, (cpx<float>*)c->plane, c->rank * c->nyl, c->nyl);
@@ -630,10 +658,35 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
         RF_CUDA(cudaGetLastError());
       }
       q.plane = (const cpx<float>*)c->plane;
+      q.z_base = 0;
       int e = 0;
       pipe::K1PMaps mout;
       memset(&mout, 0, sizeof(mout));
       c->pass2_done = false;
+      if (c->ck_cur >= 0) {
+        // one chunk of columns into its contiguous block of the send buffer
+        const int wc = nzc / c->ck_n;
+        q.z_base = c->ck_cur * wc;
+        q.nxl = c->nx;
+        char* base = (char*)c->send + (size_t)c->ck_cur * c->nx * c->nyl * wc * sizeof(cpx<float>);
+        RF_DISPATCH_PIPE(c->nx, {
+          const int tz = PipeLaunch<NN>::tile_cols();
+          q.ztiles = wc / tz;
+          q.ntiles = c->nyl * q.ztiles;
+          uint64_t sout[2] = {(uint64_t)wc * 8, (uint64_t)c->nyl * wc * 8};
+          uint64_t dout[3] = {(uint64_t)2 * wc, (uint64_t)c->nyl, (uint64_t)c->nx};
+          uint32_t bout[3] = {(uint32_t)2 * tz, 1, (uint32_t)PipeLaunch<NN>::box_rows()};
+          int e2 = make_tensor_map(&mout.m[0], base, 3, dout, sout, bout);
+          if (e2) return e2;
+          const bool twocta = c->k1q && PipeLaunch<NN>::k1q_fits(c->lut_n);
+          int grid = std::min(q.ntiles, (twocta ? 2 : PipeLaunch<NN>::ctas_per_sm()) * c->num_sms);
+          e = twocta ? PipeLaunch<NN>::k1q(c->noise != nullptr, potential != 0, mout, q, grid, c->stream)
+                     : PipeLaunch<NN>::k1p(c->noise != nullptr, potential != 0, mout, q, grid, c->stream);
+        });
+        c->launches++;
+        RF_CUDA(e);
+        return RF_OK;
+      }
       if (c->fuse12 && c->world == 1 && !c->direct && c->nx == c->ny && (c->nx == 512 || c->nx == 1024) &&
           !c->noise && c->hinge_hi >= c->hinge_lo) {
         bool launched = false;
@@ -765,6 +818,7 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
 
 extern "C" int rf_generate_xpass(rf_ctx* c, uint64_t seed, int potential) {
   if (!c) return fail(RF_ERR_ARG, "null ctx");
+  c->last_chunked = false;
   if (!c->have_power) return fail(RF_ERR_STATE, "rf_generate_xpass: call rf_set_power first");
   return c->dtype == RF_F32 ? xpass_impl<float>(c, seed, potential) : xpass_impl<double>(c, seed, potential);
 }
@@ -829,6 +883,7 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
         q.tw = (const cpx<float>*)c->tw_y;
         q.rows_per_src = p2.rows_per_src;
         q.out = (cpx<float>*)p2.out; q.out_outer = p2.out_outer; q.out_row = p2.out_row;
+        q.z_out_base = 0;
         CUtensorMap min, mout;
         RF_DISPATCH_PIPE(c->ny, {
           const int tz = PipeLaunch<NN>::tile_cols();
@@ -1014,6 +1069,166 @@ extern "C" int rf_finish_yz(rf_ctx* c, const double* zscale, int want_stats) {
                               : finish_generic_with_scale<double>(c, zscale, want_stats);
   return c->dtype == RF_F32 ? finish_impl<float>(c, zscale, want_stats)
                             : finish_impl<double>(c, zscale, want_stats);
+}
+
+// ------------------------------------------------------------------------------------------
+// chunked exchange: pass 1 / copy-engine exchange / pass 2 per chunk of packed z columns
+// ------------------------------------------------------------------------------------------
+static int pipe_tile_cols(int n) {
+  RF_DISPATCH_PIPE(n, { return PipeLaunch<NN>::tile_cols(); });
+  return 0;
+}
+static bool chunk_supported(rf_ctx* c, int nchunks) {
+  if (!c->pipe || c->dtype != RF_F32 || !c->hinge_ok || c->noise) return false;
+  if (c->nx > 4096 || c->ny > 4096 || c->nx < 64 || c->ny < 64) return false;
+  const int nzc = c->nz / 2;
+  if (nchunks < 1 || nzc % nchunks) return false;
+  const int wc = nzc / nchunks;
+  const int t1 = pipe_tile_cols(c->nx), t2 = pipe_tile_cols(c->ny);   // a chunk holds whole tiles
+  return t1 > 0 && t2 > 0 && wc % t1 == 0 && wc % t2 == 0;
+}
+
+extern "C" int rf_chunk_config(rf_ctx* c, int nchunks) {
+  if (!c) return fail(RF_ERR_ARG, "null ctx");
+  if (nchunks <= 0) {
+    RF_CUDA(cudaStreamSynchronize(c->stream));
+    if (c->send) cudaFree(c->send);
+    c->send = nullptr;
+    c->ck_n = 0;
+    c->ck_cur = -1;
+    return RF_OK;
+  }
+  if (!c->have_power) return fail(RF_ERR_STATE, "rf_chunk_config: call rf_set_power first");
+  if (!chunk_supported(c, nchunks))
+    return fail(RF_ERR_ARG, "rf_chunk_config: grid / table / chunk count not supported by the chunked path");
+  if (c->nx > 1024) {
+    const bool fits = c->nx == 2048 ? PipeLaunch<2048>::k1p_fits(c->lut_n) : PipeLaunch<4096>::k1p_fits(c->lut_n);
+    if (!fits) return fail(RF_ERR_ARG, "rf_chunk_config: sigma table too large for the pass-1 kernel");
+  }
+  if (!c->send) RF_CUDA(cudaMalloc(&c->send, (size_t)c->nx * c->nyl * (c->nz / 2) * sizeof(cpx<float>)));
+  if (!c->comm) RF_CUDA(cudaStreamCreateWithFlags(&c->comm, cudaStreamNonBlocking));
+  if (!c->ev_k1) RF_CUDA(cudaEventCreateWithFlags(&c->ev_k1, cudaEventDisableTiming));
+  if (!c->ev_x) RF_CUDA(cudaEventCreateWithFlags(&c->ev_x, cudaEventDisableTiming));
+  if (!c->ev_s) RF_CUDA(cudaEventCreateWithFlags(&c->ev_s, cudaEventDisableTiming));
+  c->ck_n = nchunks;
+  c->ck_cur = -1;
+  return RF_OK;
+}
+
+extern "C" void* rf_comm_stream(rf_ctx* c) { return c ? (void*)c->comm : nullptr; }
+
+// comm stream waits for everything queued on the compute stream so far (start of a step: the
+// previous step's pass 2 has finished reading the receive buffer once this has run)
+extern "C" int rf_chunk_begin_step(rf_ctx* c) {
+  if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_begin_step: chunked path not configured");
+  RF_CUDA(cudaEventRecord(c->ev_s, c->stream));
+  RF_CUDA(cudaStreamWaitEvent(c->comm, c->ev_s, 0));
+  return RF_OK;
+}
+
+extern "C" int rf_chunk_xpass(rf_ctx* c, uint64_t seed, int potential, int chunk) {
+  if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_xpass: chunked path not configured");
+  if (chunk < 0 || chunk >= c->ck_n) return fail(RF_ERR_ARG, "rf_chunk_xpass: bad chunk");
+  if (c->timing && (int)c->ck_ev.size() != 4 * c->ck_n) {
+    for (cudaEvent_t ev : c->ck_ev) cudaEventDestroy(ev);
+    c->ck_ev.assign((size_t)4 * c->ck_n, nullptr);
+    for (auto& ev : c->ck_ev) RF_CUDA(cudaEventCreate(&ev));
+  }
+  const bool tm = c->timing && !c->ck_ev.empty();
+  c->last_chunked = true;
+  c->ck_cur = chunk;
+  if (tm) cudaEventRecord(c->ck_ev[chunk * 2], c->stream);
+  int e = xpass_impl<float>(c, seed, potential);
+  if (tm) cudaEventRecord(c->ck_ev[chunk * 2 + 1], c->stream);
+  c->ck_cur = -1;
+  if (e) return e;
+  RF_CUDA(cudaEventRecord(c->ev_k1, c->stream));
+  return RF_OK;
+}
+
+// copy engines: block d of send[chunk] -> block `rank` of recv[chunk] on rank d (peer memory)
+extern "C" int rf_chunk_exchange(rf_ctx* c, int chunk) {
+  if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_exchange: chunked path not configured");
+  if (chunk < 0 || chunk >= c->ck_n) return fail(RF_ERR_ARG, "rf_chunk_exchange: bad chunk");
+  RF_CUDA(cudaStreamWaitEvent(c->comm, c->ev_k1, 0));
+  if (c->world == 1) return RF_OK;   // pass 2 reads the send buffer directly
+  const size_t wc = (size_t)(c->nz / 2) / c->ck_n;
+  const size_t block = (size_t)c->nxl * c->nyl * wc * sizeof(cpx<float>);
+  const size_t chunk_off = (size_t)chunk * c->world * block;
+  for (int i = 0; i < c->world; ++i) {
+    const int d = (c->rank + 1 + i) % c->world;   // staggered: no receiver is everybody's first target
+    char* peer = (char*)(c->peer_recv[d] ? c->peer_recv[d] : (d == c->rank ? c->recv : nullptr));
+    if (!peer) return fail(RF_ERR_STATE, "rf_chunk_exchange: receive buffer of a peer is not mapped");
+    RF_CUDA(cudaMemcpyAsync(peer + chunk_off + (size_t)c->rank * block,
+                            (const char*)c->send + chunk_off + (size_t)d * block, block,
+                            cudaMemcpyDeviceToDevice, c->comm));
+  }
+  return RF_OK;
+}
+
+// call after the cross-rank fence for this chunk has been queued on the comm stream
+extern "C" int rf_chunk_arrived(rf_ctx* c, int chunk) {
+  if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_arrived: chunked path not configured");
+  if (chunk < 0 || chunk >= c->ck_n) return fail(RF_ERR_ARG, "rf_chunk_arrived: bad chunk");
+  // one event per chunk: the compute stream only waits for it when pass 2 of this chunk is
+  // queued (rf_chunk_pass2), after pass 1 of the following chunks
+  if ((int)c->ev_xc.size() < c->ck_n) {
+    const size_t old = c->ev_xc.size();
+    c->ev_xc.resize(c->ck_n, nullptr);
+    for (size_t k = old; k < c->ev_xc.size(); ++k)
+      RF_CUDA(cudaEventCreateWithFlags(&c->ev_xc[k], cudaEventDisableTiming));
+  }
+  RF_CUDA(cudaEventRecord(c->ev_xc[chunk], c->comm));
+  return RF_OK;
+}
+
+extern "C" int rf_chunk_pass2(rf_ctx* c, int chunk) {
+  if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_pass2: chunked path not configured");
+  if (chunk < 0 || chunk >= c->ck_n) return fail(RF_ERR_ARG, "rf_chunk_pass2: bad chunk");
+  if (chunk >= (int)c->ev_xc.size() || !c->ev_xc[chunk])
+    return fail(RF_ERR_STATE, "rf_chunk_pass2: rf_chunk_arrived has not been called for this chunk");
+  RF_CUDA(cudaStreamWaitEvent(c->stream, c->ev_xc[chunk], 0));
+  const int nzc = c->nz / 2, wc = nzc / c->ck_n;
+  pipe::K2PParams q;
+  q.tw = (const cpx<float>*)c->tw_y;
+  q.out = (cpx<float>*)c->field;
+  q.out_outer = (long long)c->ny * nzc;
+  q.out_row = nzc;
+  q.z_out_base = chunk * wc;
+  q.tile0 = 0;
+  const size_t chunk_elems = (size_t)c->nx * c->nyl * wc;
+  const cpx<float>* in = (const cpx<float>*)(c->world > 1 ? c->recv : c->send) + (size_t)chunk * chunk_elems;
+  q.rows_per_src = c->world > 1 ? c->nyl : c->ny;
+  int e = 0;
+  CUtensorMap min, mout;
+  RF_DISPATCH_PIPE(c->ny, {
+    const int tz = PipeLaunch<NN>::tile_cols();
+    q.ztiles = wc / tz;
+    q.ntiles = c->nxl * q.ztiles;
+    q.box_rows = std::min(PipeLaunch<NN>::box_rows(), q.rows_per_src);
+    const int nsrc = c->ny / q.rows_per_src;
+    // [src][nxl][rows_per_src][wc]; single GPU: [nx][ny][wc]
+    uint64_t din[4] = {(uint64_t)2 * wc, (uint64_t)q.rows_per_src, (uint64_t)c->nxl, (uint64_t)nsrc};
+    uint64_t sin[3] = {(uint64_t)wc * 8, (uint64_t)q.rows_per_src * wc * 8,
+                       (uint64_t)c->nxl * q.rows_per_src * wc * 8};
+    uint32_t bin[4] = {(uint32_t)2 * tz, (uint32_t)q.box_rows, 1, 1};
+    int e2 = make_tensor_map(&min, (void*)in, 4, din, sin, bin);
+    if (e2) return e2;
+    uint64_t dout[3] = {(uint64_t)2 * nzc, (uint64_t)c->ny, (uint64_t)c->nxl};
+    uint64_t sout[2] = {(uint64_t)nzc * 8, (uint64_t)c->ny * nzc * 8};
+    uint32_t bout[3] = {(uint32_t)2 * tz, (uint32_t)PipeLaunch<NN>::box_rows(), 1};
+    e2 = make_tensor_map(&mout, c->field, 3, dout, sout, bout);
+    if (e2) return e2;
+    const int grid = std::min(q.ntiles, PipeLaunch<NN>::ctas_per_sm() * c->num_sms);
+    const bool tm = c->timing && (int)c->ck_ev.size() == 4 * c->ck_n;
+    if (tm) cudaEventRecord(c->ck_ev[(c->ck_n + chunk) * 2], c->stream);
+    e = PipeLaunch<NN>::k2p(min, mout, q, grid, c->stream);
+    if (tm) cudaEventRecord(c->ck_ev[(c->ck_n + chunk) * 2 + 1], c->stream);
+  });
+  c->launches++;
+  RF_CUDA(e);
+  if (chunk == c->ck_n - 1) c->pass2_done = true;   // rf_finish_yz now runs pass 3 only
+  return RF_OK;
 }
 
 extern "C" int rf_generate_delta(rf_ctx* c, uint64_t seed, int potential, const double* zscale,

@@ -268,7 +268,7 @@ k2b_strided_fft(const __grid_constant__ CUtensorMap map_in, const K2PParams p) {
     __syncthreads();
     if (tid == 0 && t + step < p.ntiles) load_rows(t + step, kSplit, N, buf, &full[1]);
     const int tt = t + p.tile0;
-    cpx<float>* const outp = p.out + (size_t)(tt / p.ztiles) * p.out_outer + (tt % p.ztiles) * TZ;
+    cpx<float>* const outp = p.out + (size_t)(tt / p.ztiles) * p.out_outer + (tt % p.ztiles) * TZ + p.z_out_base;
     sfor<0, G::IC>([&](auto qi) {
       constexpr int q = decltype(qi)::value;
       const int w = tid + q * kThreads;
@@ -322,7 +322,7 @@ k1b_generate_xfft(const __grid_constant__ K1PMaps maps, const K1PParams p) {
       constexpr int qn = decltype(qi)::value;
       const int w = tid + qn * kThreads;
       const int c = w % TZ, j = w / TZ;
-      const int iz = z0 + c;
+      const int iz = p.z_base + z0 + c;
       if (iz == 0) {
         const cpx<float>* pp = p.plane + (size_t)j * p.ny_local + iyl;
         sfor<0, R1>([&](auto mi) {

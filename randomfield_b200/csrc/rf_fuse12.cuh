@@ -152,7 +152,7 @@ k12_generate_xyfft(const __grid_constant__ pipe::K1PMaps maps, const __grid_cons
       const int iyl = r / p.zc, zt = chunk * p.zc + (r - iyl * p.zc);
       const int z0 = zt * TZ;
       const int iy = k1.y0 + iyl;
-      const int iz = z0 + c;
+      const int iz = k1.z_base + z0 + c;
       cpx<float> v[R1];
       if (iz == 0) {
         const cpx<float>* pp = k1.plane + (size_t)j * k1.ny_local + iyl;

@@ -493,6 +493,7 @@ struct K2PParams {
   int ztiles;              // ncols / TZ
   int rows_per_src;        // rows of a line held by one source block (N when single GPU)
   int box_rows;            // rows per TMA box = min(256, rows_per_src)
+  int z_out_base;          // column offset of this launch in the output (chunked runs)
   // output addressing for kernels that store from registers (rf_big.cuh): element
   // out[outer * out_outer + row * out_row + column]
   cpx<float>* out;
@@ -550,7 +551,7 @@ k2p_strided_fft(const __grid_constant__ CUtensorMap map_in, const __grid_constan
         mbar_wait(&done[b], (i >> 1) & 1);
         const int o = (t + p.tile0) / p.ztiles, z0 = ((t + p.tile0) % p.ztiles) * P::TZ;
         for (int r0 = 0; r0 < N; r0 += P::kBoxRows)
-          tma_store_3d(&map_out, dense0 + b * kDenseElems + r0 * P::TZ, 2 * z0, r0, o);
+          tma_store_3d(&map_out, dense0 + b * kDenseElems + r0 * P::TZ, 2 * (z0 + p.z_out_base), r0, o);
         bulk_commit();
         const int t2 = t + 2 * step;
         if (t2 < p.ntiles) {
@@ -593,6 +594,8 @@ struct K1PParams {
   int ny_local, y0;        // y-slab owned by this rank; y0 = first global iy
   int ntiles, ztiles;      // ny_local * ztiles, (nz/2) / TZ
   int nxl;                 // rows per destination rank (== NX when not slab-decomposed)
+  int z_base;              // first global packed column of this launch (chunked runs); tile and
+                           // store coordinates are relative to it
 };
 
 // one store map per destination rank: (2*ncols floats, ny_local, nx/G) over this rank's source
@@ -639,7 +642,7 @@ k1p_generate_xfft(const __grid_constant__ K1PMaps maps, const K1PParams p) {
     const int iy = p.y0 + iyl;
 
     step_a<NX, P::R1, L>(work, tid, P::TZ, twr, [&](cpx<float>(&v)[P::R1], int jj, int cc) {
-      const int iz = z0 + cc;
+      const int iz = p.z_base + z0 + cc;
       if (iz == 0) {
         // packed column (iz=0 plane) + i*(iz=nz/2 plane): precomputed by gen_packed_plane_kernel
         const cpx<float>* pp = p.plane + (size_t)jj * p.ny_local + iyl;
@@ -753,7 +756,7 @@ k1q_generate_xfft(const __grid_constant__ K1PMaps maps, const K1PParams p) {
   for (int t = first; t < p.ntiles; t += step) {
     const int iyl = t / p.ztiles, z0 = (t % p.ztiles) * TZ;
     const int iy = p.y0 + iyl;
-    const int iz = z0 + c;
+    const int iz = p.z_base + z0 + c;
     cpx<float> v[R1];
     if (iz == 0) {
       // packed column (iz=0 plane) + i*(iz=nz/2 plane): precomputed by gen_packed_plane_kernel

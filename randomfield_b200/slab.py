@@ -52,7 +52,7 @@ class SlabEngine(object):
     """The device side of a slab-decomposed Generator on this rank."""
 
     def __init__(self, nx, ny, nz, spacing, power, smoothing=0.0, dtype=np.float32, group=None,
-                 direct=None):
+                 direct=None, chunks=None):
         import torch
         import torch.distributed as dist
         self.group = group
@@ -69,13 +69,37 @@ class SlabEngine(object):
         if self.world > 1:
             self._send = self.engine.torch_view(_lib.RF_BUF_FIELD, self._xfer_bytes)
             self._recv = self.engine.torch_view(_lib.RF_BUF_RECV, self._xfer_bytes)
-        # direct exchange: pass 1 stores into the peers' receive buffers over NVLink (CUDA IPC
-        # mappings), the all-to-all disappears; two tiny all-reduces fence the receive buffers
-        if direct is None:
-            direct = os.environ.get("RF_DIRECT", "1") != "0"
-        self.direct = bool(direct) and 2 <= self.world <= 8
+        # Exchange modes (env RF_EXCHANGE / arguments):
+        #   "chunked": pass 1, copy-engine pushes into the peers' receive buffers and pass 2 are
+        #              pipelined over chunks of z columns (default; rf_chunk_* in the C ABI);
+        #   "direct" : pass 1 stores into the peers' receive buffers over NVLink, no collective;
+        #   "nccl"   : one NCCL all-to-all between pass 1 and pass 2.
+        # "chunked" and "direct" map the peers' receive buffers through CUDA IPC and fence them
+        # with 1-element all-reduces.
+        mode = os.environ.get("RF_EXCHANGE", "")
+        if direct is not None:
+            mode = "direct" if direct else (mode if mode in ("nccl", "chunked") else "nccl")
+        elif not mode:
+            mode = "direct" if os.environ.get("RF_DIRECT") == "1" else (
+                "nccl" if os.environ.get("RF_DIRECT") == "0" else "chunked")
+        if not 2 <= self.world <= 8:
+            mode = "single"
+        self.nchunks = 0
+        if mode == "chunked":
+            want = int(os.environ.get("RF_CHUNKS", "0")) or (chunks or 8)
+            while want > 1:
+                try:
+                    self.engine.chunk_config(want)
+                    self.nchunks = want
+                    break
+                except (RuntimeError, ValueError):
+                    want //= 2
+            if not self.nchunks:
+                mode = "nccl"
+        self.mode = mode
+        self.direct = mode == "direct"
         self._peer_ptrs = []
-        if self.direct:
+        if mode in ("direct", "chunked"):
             handles = [None] * self.world
             dist.all_gather_object(handles, self.engine.ipc_export(_lib.RF_BUF_RECV), group=group)
             for r, h in enumerate(handles):
@@ -84,8 +108,11 @@ class SlabEngine(object):
                 ptr = _lib.Engine.ipc_open(h)
                 self._peer_ptrs.append(ptr)
                 self.engine.set_peer_recv(r, ptr)
-            self.engine.set_direct(True)
+            if self.direct:
+                self.engine.set_direct(True)
             self._fence = torch.zeros(1, device="cuda")
+            if mode == "chunked":
+                self._comm = torch.cuda.ExternalStream(self.engine.comm_stream)
 
     @property
     def exchange_bytes(self):
@@ -100,7 +127,23 @@ class SlabEngine(object):
             if self.world == 1:
                 self.engine.generate_delta(seed, potential, zscale, want_stats)
             else:
-                if self.direct:
+                if self.mode == "chunked":
+                    eng, q = self.engine, self._comm
+                    eng.chunk_begin_step()
+                    with torch.cuda.stream(q):
+                        # peers have finished reading their receive buffers (previous step)
+                        dist.all_reduce(self._fence, group=self.group)
+                    for c in range(self.nchunks):
+                        eng.chunk_xpass(seed, potential, c)
+                        eng.chunk_exchange(c)
+                        with torch.cuda.stream(q):
+                            # every rank's copies of chunk c have landed
+                            dist.all_reduce(self._fence, group=self.group)
+                        eng.chunk_arrived(c)
+                        if c >= 1:
+                            eng.chunk_pass2(c - 1)
+                    eng.chunk_pass2(self.nchunks - 1)
+                elif self.direct:
                     # peers have finished reading their receive buffers (previous step) ...
                     dist.all_reduce(self._fence, group=self.group)
                     self.engine.generate_xpass(seed, potential)
@@ -128,7 +171,7 @@ class SlabEngine(object):
 
 
 def run_virtual_slabs(nx, ny, nz, spacing, power, seed, world, smoothing=0.0, dtype=np.float32,
-                      potential=False, zscale=None, direct=False):
+                      potential=False, zscale=None, direct=False, chunks=0):
     """All `world` ranks of the slab pipeline driven from ONE process on ONE GPU: each rank's
     engine generates its y-slab, the all-to-all is done with device copies between the
     engines' buffers, each rank finishes its x-slab.  Returns (field (nx, ny, nz), mean, std).
@@ -144,11 +187,30 @@ def run_virtual_slabs(nx, ny, nz, spacing, power, seed, world, smoothing=0.0, dt
             for r, peer in enumerate(engines):
                 e.set_peer_recv(r, peer.device_ptr(_lib.RF_BUF_RECV))
             e.set_direct(True)
+    if chunks:
+        # chunked exchange: every rank's pass 1 + copy-engine pushes, then every rank's pass 2
+        for e in engines:
+            e.set_power(k, sig, spacing)
+            for r, peer in enumerate(engines):
+                e.set_peer_recv(r, peer.device_ptr(_lib.RF_BUF_RECV))
+            e.chunk_config(chunks)
+        for e in engines:
+            e.chunk_begin_step()
+            for c in range(chunks):
+                e.chunk_xpass(seed, potential, c)
+                e.chunk_exchange(c)
+        torch.cuda.synchronize()
+        for e in engines:
+            for c in range(chunks):
+                e.chunk_arrived(c)
+                e.chunk_pass2(c)
     for e in engines:
+        if chunks:
+            break
         e.set_power(k, sig, spacing)
         e.generate_xpass(seed, potential)
         e.sync()
-    if world > 1 and not direct:
+    if world > 1 and not direct and not chunks:
         sends = [e.torch_view(_lib.RF_BUF_FIELD, xfer).view(world, -1) for e in engines]
         recvs = [e.torch_view(_lib.RF_BUF_RECV, xfer).view(world, -1) for e in engines]
         for d in range(world):

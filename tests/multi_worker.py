@@ -15,11 +15,12 @@ out = sys.argv[1]
 local = int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-eng = SlabEngine(128, 128, 64, 2.0, powertools.load_default_power())
+eng = SlabEngine(256, 256, 128, 2.0, powertools.load_default_power())
 eng.generate(42)
 mean, std = eng.global_stats()
 np.save(os.path.join(out, "rank%d.npy" % dist.get_rank()), eng.local_field())
 if dist.get_rank() == 0:
     open(os.path.join(out, "std.txt"), "w").write(repr(std))
+    open(os.path.join(out, "mode.txt"), "w").write(eng.mode)
 dist.barrier()
 dist.destroy_process_group()

@@ -39,6 +39,20 @@ def test_direct_exchange_bit_identical(shape):
         assert np.array_equal(got, ref), "world=%d" % world
 
 
+@pytest.mark.parametrize("shape,chunks", [((256, 256, 128), 4), ((128, 256, 128), 2), ((2048, 128, 128), 2),
+                                          ((128, 4096, 128), 2)])
+def test_chunked_exchange_bit_identical(shape, chunks):
+    """Pass 1 / copy-engine exchange / pass 2 pipelined over chunks of z columns (rf_chunk_*)
+    gives the same bits as the unchunked single-rank run, for every decomposition."""
+    from randomfield_b200 import slab
+    power = oracle.load_default_power()
+    ref, _, std1 = slab.run_virtual_slabs(*shape, 2.0, power, seed=99, world=1)
+    for world in (1, 2, 8):
+        got, _, std = slab.run_virtual_slabs(*shape, 2.0, power, seed=99, world=world, chunks=chunks)
+        assert np.array_equal(got, ref), "world=%d" % world
+        assert abs(std - std1) <= 1e-9 * std1
+
+
 def test_slab_field_matches_oracle():
     """and the decomposed field is the right field: Philox restatement + numpy irfftn."""
     from randomfield_b200 import slab
@@ -61,21 +75,20 @@ def test_potential_and_zscale_across_decompositions():
     assert np.array_equal(got, ref)
 
 
-def test_fused_pass12_kernel_bit_identical(monkeypatch):
-    """The opt-in fused pass-1 + pass-2 kernel (RF_FUSE12=1, rf_fuse12.cuh) gives the same bits as
-    the separate kernels."""
+def test_fused_pass12_kernel_matches(monkeypatch):
+    """The opt-in fused pass-1 + pass-2 kernel (RF_FUSE12=1, rf_fuse12.cuh).  Its pass-2 warp group
+    runs a radix 16x8x8 plan where k2p runs 32x32, so the field agrees to rounding (rel. RMS
+    <= 1e-6), not bit for bit: one more reason it stays opt-in."""
     from randomfield_b200 import slab
     power = oracle.load_default_power()
     shape = (512, 512, 64)
-    monkeypatch.setenv("RF_FUSE12", "0")
-    ref, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1)
-    monkeypatch.setenv("RF_FUSE12", "1")
-    got, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1)
-    assert np.array_equal(got, ref)
-    gotp, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1, potential=True)
-    monkeypatch.setenv("RF_FUSE12", "0")
-    refp, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1, potential=True)
-    assert np.array_equal(gotp, refp)
+    for potential in (False, True):
+        monkeypatch.setenv("RF_FUSE12", "0")
+        ref, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1, potential=potential)
+        monkeypatch.setenv("RF_FUSE12", "1")
+        got, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1, potential=potential)
+        err = np.sqrt(np.mean((got.astype(np.float64) - ref) ** 2)) / ref.std(dtype=np.float64)
+        assert err <= 1e-6
 
 
 def _ngpu():
@@ -84,18 +97,21 @@ def _ngpu():
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs two GPUs")
-@pytest.mark.parametrize("direct", ["1", "0"])
+@pytest.mark.parametrize("direct", ["1", "0", "chunked"])
 def test_nccl_two_ranks_matches_single(tmp_path, direct):
-    """Real one-process-per-GPU run (direct peer stores, and the NCCL all-to-all): rank slabs
-    written to disk, compared with world=1."""
+    """Real one-process-per-GPU run (direct peer stores, the NCCL all-to-all, and the chunked
+    copy-engine exchange): rank slabs written to disk, compared with world=1."""
     script = os.path.join(ROOT, "tests", "multi_worker.py")
     out = str(tmp_path)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
-           "--master-addr", "127.0.0.1", "--master-port", "29533" if direct == "1" else "29535", script, out]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=dict(os.environ, RF_DIRECT=direct))
+           "--master-addr", "127.0.0.1", "--master-port", {"1": "29533", "0": "29535"}.get(direct, "29537"), script, out]
+    env = dict(os.environ, RF_EXCHANGE="chunked", RF_CHUNKS="2") if direct == "chunked" else dict(
+        os.environ, RF_DIRECT=direct)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0, r.stdout + r.stderr
     from randomfield_b200 import slab
-    ref, _, std1 = slab.run_virtual_slabs(128, 128, 64, 2.0, oracle.load_default_power(), seed=42, world=1)
+    assert open(os.path.join(out, "mode.txt")).read() == {"1": "direct", "0": "nccl"}.get(direct, direct)
+    ref, _, std1 = slab.run_virtual_slabs(256, 256, 128, 2.0, oracle.load_default_power(), seed=42, world=1)
     got = np.concatenate([np.load(os.path.join(out, "rank%d.npy" % r)) for r in range(2)], axis=0)
     assert np.array_equal(got, ref)
     std = float(open(os.path.join(out, "std.txt")).read())
