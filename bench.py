@@ -180,7 +180,11 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("NCCL_DEBUG", "WARN")   # keeps NCCL's version banner off stdout (one JSON line)
+        # NCCL prints its version banner on stdout at the first collective: route fd 1 to stderr
+        # until the JSON line, which must be the only thing on stdout
+        sys.stdout.flush()
+        args._saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     grid = parse_grid(args)
     nx, ny, nz = grid
@@ -310,8 +314,12 @@ def run_ours(args):
             "value": n ** 3 / sec / 1e6, "unit": UNIT, "cores": 1, "kind": "port",
             "sample": "%d^3 grid, one pass of the reference algorithm (oracle port: numpy pocketfft "
                       "irfftn + MT19937 normal), %.1f s" % (n, sec)}
-    print(json.dumps(line))
+    if getattr(args, "_saved_stdout", None) is not None:
+        sys.stdout.flush()
+        os.dup2(args._saved_stdout, 1)
+    print(json.dumps(line), flush=True)
     if world > 1:
+        os.dup2(2, 1)
         dist.destroy_process_group()
     return 0
 
