@@ -141,6 +141,16 @@ int rf_ipc_close(void* ptr);
 int rf_set_peer_recv(rf_ctx* ctx, int rank, void* recv_ptr);
 int rf_set_direct(rf_ctx* ctx, int enabled);
 
+/* Lensing potential psi(r) -- Generator.calculate_lensing_potential (generate.py:353-418):
+ * for every slice i, scipy.integrate.simps over DC of -2 (cotK_j - cotK_{i-1}) dPhi_j,
+ * j in [i_min, i); slices below i_min are zeroed.  In place on the real-space field (normally the
+ * light-cone Newtonian potential), one O(nz) parity-split prefix sum per line of sight.
+ * tables5 = 5 contiguous float64 arrays of nz entries built by the caller from DC and cotK:
+ *   cotK[j]; a[j], b[j], d[j] = Simpson weights of the three-point panel (j-2, j-1, j) on the
+ *   abscissae DC (0 for j < 2); t[j] = (DC[j] - DC[j-1]) / 2 (0 for j = 0).
+ * (randomfield_b200.generate.lensing_tables restates the weights of scipy.integrate.simps.) */
+int rf_lensing(rf_ctx* ctx, int i_min, const double* tables5);
+
 /* Chunked exchange (slab decomposition): the packed z columns (nz/2) are cut into `nchunks`
  * chunks.  Pass 1 of chunk c writes a contiguous send block, the copy engines push its G
  * blocks into the peers' receive buffers (rf_set_peer_recv pointers) on the context's comm

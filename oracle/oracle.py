@@ -425,3 +425,77 @@ def philox_kfield(shape, spacing, power, seed, smoothing=0.0, potential=False):
         out[:, :, iz] = plane
     out[0, 0, 0] = 0.0
     return out, bins
+
+
+# ------------------------------------------------------------------------------------------
+# part 3: lensing potential.  Parity status: UNPINNED -- the
+# reference's calculate_lensing_potential cannot run here (astropy absent; scipy 1.18 has no
+# integrate.simps), so this is a restatement of generate.py:374-410 on top of a restatement of
+# the third-party rule it calls.
+# ------------------------------------------------------------------------------------------
+def _basic_simps(y, start, stop, x):
+    """Composite Simpson over the panels starting at start, start+2, ..., < stop on non-uniform
+    abscissae (last axis).  Restates scipy.integrate._quadrature._basic_simps as shipped up to
+    scipy 1.5 (the rule `simps` used when the reference was written: unpinned dependency,
+    README 'scipy'); three-point weights hsum/6 * (2 - h1/h0, hsum^2/(h0 h1), 2 - h0/h1)."""
+    if stop <= start:
+        return np.zeros(y.shape[:-1], dtype=np.float64)
+    h = np.diff(x)
+    h0, h1 = h[start:stop:2], h[start + 1:stop + 1:2]
+    hsum, hprod, h0divh1 = h0 + h1, h0 * h1, h0 / h1
+    tmp = hsum / 6.0 * (y[..., start:stop:2] * (2 - 1.0 / h0divh1) +
+                        y[..., start + 1:stop + 1:2] * hsum * hsum / hprod +
+                        y[..., start + 2:stop + 2:2] * (2 - h0divh1))
+    return np.sum(tmp, axis=-1)
+
+
+def simps_old(y, x):
+    """scipy.integrate.simps(y, x, axis=-1, even='avg') as it behaved when the reference called
+    it (generate.py:408): Simpson's rule for an odd number of samples; for an even number the
+    average of (Simpson on the first N-1 samples + trapezoid on the last interval) and
+    (trapezoid on the first interval + Simpson on the last N-1 samples)."""
+    y = np.asarray(y, dtype=np.float64)
+    x = np.asarray(x, dtype=np.float64)
+    n = y.shape[-1]
+    if n % 2 == 0:
+        val = 0.5 * (x[-1] - x[-2]) * (y[..., -1] + y[..., -2])
+        result = _basic_simps(y, 0, n - 3, x)
+        val = val + 0.5 * (x[1] - x[0]) * (y[..., 1] + y[..., 0])
+        result = result + _basic_simps(y, 1, n - 2, x)
+        return result / 2.0 + val / 2.0
+    return _basic_simps(y, 0, n - 2, x)
+
+
+def cot_k(DC, DA, Ok0):
+    """generate.py:380-394: cosK(D) / D_A, with cotK[0] = 1."""
+    H0, clight_km_s = 100.0, 299792.458
+    K = -Ok0 * (H0 / clight_km_s) ** 2
+    if K < 0:
+        cosK = np.cosh(np.sqrt(-K) * DC)
+    elif K > 0:
+        cosK = np.cos(np.sqrt(K) * DC)
+    else:
+        cosK = np.ones_like(DA, dtype=float)
+    cotK = np.ones_like(cosK)
+    cotK[1:] = cosK[1:] / DA[1:]
+    return cotK
+
+
+def lensing_potential(dphi, DC, DA, Ok0=0.0, i_min=None):
+    """generate.py:374-410, loop for loop: psi[:, :, i-1] = simps(-2 (cotK_j - cotK_{i-1}) dPhi_j,
+    x=DC_j, j in [i_min, i)) for i = nDC ... i_min+1; slices below i_min are zero.  The result
+    has dPhi's dtype (the reference stores the float64 integral into an array like dPhi)."""
+    dphi = np.asarray(dphi)
+    nDC = DC.size
+    if i_min is None:
+        i_min = nDC // 32
+    if i_min < 0 or i_min >= nDC:
+        raise ValueError('Invalid i_min {}. Expected 0 - {}.'.format(i_min, nDC - 1))
+    cotK = cot_k(DC, DA, Ok0)
+    psi = np.empty_like(dphi)
+    for i in range(nDC, i_min, -1):
+        y = dphi[:, :, i_min:i].astype(np.float64) * (-2 * (cotK[i_min:i] - cotK[i - 1]))
+        psi[:, :, i - 1] = simps_old(y, DC[i_min:i])
+    if i_min > 0:
+        psi[:, :, :i_min] = 0.
+    return psi

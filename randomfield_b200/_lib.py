@@ -55,6 +55,7 @@ SIGNATURES = {
     "rf_ipc_close": (_c.c_int, [_P]),
     "rf_set_peer_recv": (_c.c_int, [_P, _c.c_int, _P]),
     "rf_set_direct": (_c.c_int, [_P, _c.c_int]),
+    "rf_lensing": (_c.c_int, [_P, _c.c_int, _P]),
     "rf_chunk_config": (_c.c_int, [_P, _c.c_int]),
     "rf_comm_stream": (_c.c_void_p, [_P]),
     "rf_chunk_begin_step": (_c.c_int, [_P]),
@@ -260,6 +261,13 @@ class Engine:
 
     def set_direct(self, enabled=True):
         check(lib().rf_set_direct(self._ctx, int(bool(enabled))))
+
+    def lensing(self, i_min, tables5):
+        """In-place lensing-potential scan of the real field; tables5: (5, nz) float64."""
+        t = np.ascontiguousarray(tables5, dtype=np.float64)
+        if t.shape != (5, self.nz):
+            raise ValueError("tables5 must have shape (5, nz)")
+        check(lib().rf_lensing(self._ctx, int(i_min), ptr(t)))
 
     # ---- chunked exchange (include/rf_b200.h: rf_chunk_*) ----
     def chunk_config(self, nchunks):

@@ -10,6 +10,7 @@
 #include "../../include/rf_b200.h"
 #include "rf_generic.cuh"
 #include "rf_launch.h"
+#include "rf_lens.cuh"
 
 using namespace rf;
 
@@ -84,6 +85,7 @@ struct rf_ctx {
   bool have_power = false;
   double* noise = nullptr;
   void *zs_dev = nullptr, *da_dev = nullptr, *db_dev = nullptr;   // nz-length tables of T
+  double* lens_dev = nullptr;   // 5 * nz coefficient tables of rf_lensing
   long long launches = 0;
   bool field_is_real = false;
   bool timing = false;
@@ -181,7 +183,7 @@ extern "C" int rf_destroy(rf_ctx* c) {
   if (!c) return RF_OK;
   cudaStreamSynchronize(c->stream);
   void* ptrs[] = {c->field, c->recv, c->partials, c->stats_dev, c->tw_x, c->tw_y, c->tw_z,
-                  c->tw_zh, c->knots, c->cells, c->hinge, c->plane, c->sched, c->zt_done, c->noise, c->zs_dev, c->da_dev, c->db_dev};
+                  c->tw_zh, c->knots, c->cells, c->hinge, c->plane, c->sched, c->zt_done, c->lens_dev, c->noise, c->zs_dev, c->da_dev, c->db_dev};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   if (c->send) cudaFree(c->send);
@@ -1294,6 +1296,41 @@ extern "C" int rf_density(rf_ctx* c, int lognormal, double sigma, const double* 
   if (lognormal && !(sigma > 0)) return fail(RF_ERR_ARG, "rf_density: sigma must be > 0");
   return c->dtype == RF_F32 ? density_impl<float>(c, lognormal, sigma, growth, rho)
                             : density_impl<double>(c, lognormal, sigma, growth, rho);
+}
+
+// ------------------------------------------------------------------------------------------
+// lensing potential along the line of sight (generate.py:353-418), in place on the real field
+// ------------------------------------------------------------------------------------------
+template <typename T>
+static int lensing_impl(rf_ctx* c, int i_min, const double* tables5) {
+  const int nz = c->nz;
+  if (!c->lens_dev) RF_CUDA(cudaMalloc((void**)&c->lens_dev, sizeof(double) * 5 * nz));
+  // pageable source: staged before the call returns, ordered on the stream
+  RF_CUDA(cudaMemcpyAsync(c->lens_dev, tables5, sizeof(double) * 5 * nz, cudaMemcpyHostToDevice, c->stream));
+  RF_CUDA(cudaStreamSynchronize(c->stream));
+  LensTables tb;
+  tb.cotk = c->lens_dev; tb.pa = c->lens_dev + nz; tb.pb = c->lens_dev + 2 * nz;
+  tb.pd = c->lens_dev + 3 * nz; tb.pt = c->lens_dev + 4 * nz;
+  int warps = 16;
+  while (warps > 1 && lens_smem_bytes(nz, warps, sizeof(T)) > 112 * 1024) warps >>= 1;
+  const size_t smem = lens_smem_bytes(nz, warps, sizeof(T));
+  if (smem > 227 * 1024) return fail(RF_ERR_ARG, "rf_lensing: nz too large");
+  RF_CUDA(cudaFuncSetAttribute(lensing_scan_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const long long nlines = (long long)c->nxl * c->ny;
+  const int per_sm = std::max(1, (int)((size_t)228 * 1024 / (smem + 1024)));
+  const int grid = (int)std::min<long long>((nlines + warps - 1) / warps, (long long)c->num_sms * per_sm);
+  lensing_scan_kernel<T><<<grid, 32 * warps, smem, c->stream>>>((T*)c->field, nlines, nz, i_min, tb);
+  c->launches++;
+  c->stats_valid = false;
+  RF_CUDA(cudaGetLastError());
+  return RF_OK;
+}
+
+extern "C" int rf_lensing(rf_ctx* c, int i_min, const double* tables5) {
+  if (!c || !tables5) return fail(RF_ERR_ARG, "rf_lensing: null argument");
+  if (!c->field_is_real) return fail(RF_ERR_STATE, "rf_lensing: no real-space field");
+  if (i_min < 0 || i_min >= c->nz) return fail(RF_ERR_ARG, "rf_lensing: i_min out of range");
+  return c->dtype == RF_F32 ? lensing_impl<float>(c, i_min, tables5) : lensing_impl<double>(c, i_min, tables5);
 }
 
 extern "C" int rf_copy_field(rf_ctx* c, void* host_dst) {

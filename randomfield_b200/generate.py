@@ -52,6 +52,69 @@ class _PlanView(object):
         return self._g._host_field()
 
 
+def cot_k(DC, DA, Ok0):
+    """cotK(D) = cosK(D) / D_A(D), 1 at the observer (generate.py:380-394)."""
+    H0, clight_km_s = 100., 299792.458
+    K = -Ok0 * (H0 / clight_km_s) ** 2
+    if K < 0:
+        cosK = np.cosh(np.sqrt(-K) * DC)
+    elif K > 0:
+        cosK = np.cos(np.sqrt(K) * DC)
+    else:
+        cosK = np.ones_like(DA, dtype=float)
+    cotK = np.ones_like(cosK)
+    cotK[1:] = cosK[1:] / DA[1:]
+    return cotK
+
+
+def lensing_tables(DC, cotK):
+    """Coefficient tables of rf_lensing (include/rf_b200.h), shape (5, nz) float64: cotK; the
+    weights (a, b, d) scipy.integrate.simps gives the three samples (j-2, j-1, j) of a Simpson
+    panel on the abscissae DC -- hsum/6 * (2 - h1/h0, hsum^2 / (h0 h1), 2 - h0/h1) with
+    h0 = DC[j-1] - DC[j-2], h1 = DC[j] - DC[j-1]; and the trapezoid half-width (DC[j] - DC[j-1]) / 2."""
+    x = np.asarray(DC, dtype=np.float64)
+    nz = x.size
+    t = np.zeros((5, nz))
+    t[0] = cotK
+    h = np.diff(x)
+    if nz >= 3:
+        h0, h1 = h[:-1], h[1:]
+        hsum = h0 + h1
+        t[1, 2:] = hsum / 6.0 * (2 - h1 / h0)
+        t[2, 2:] = hsum / 6.0 * hsum * hsum / (h0 * h1)
+        t[3, 2:] = hsum / 6.0 * (2 - h0 / h1)
+    t[4, 1:] = 0.5 * h
+    return t
+
+
+def lensing_scan_host(dphi, tables, i_min):
+    """numpy restatement of the device algorithm (rf_lens.cuh): parity-split running sums of the
+    Simpson panels instead of one integral per slice.  Host logic for the CPU tests."""
+    cotk, pa, pb, pd, pt = tables
+    f = np.asarray(dphi, dtype=np.float64)
+    g = f * cotk
+    nz = f.shape[-1]
+    psi = np.zeros_like(f)
+    aE = [np.zeros(f.shape[:-1]), np.zeros(f.shape[:-1])]
+    aO = [np.zeros(f.shape[:-1]), np.zeros(f.shape[:-1])]
+    T0 = [0.0, 0.0]
+    if i_min + 1 < nz:
+        T0 = [pt[i_min + 1] * (q[..., i_min] + q[..., i_min + 1]) for q in (f, g)]
+    for j in range(i_min, nz):
+        odd = (j - i_min) & 1
+        if j >= i_min + 2:
+            for n, q in enumerate((f, g)):
+                pan = pa[j] * q[..., j - 2] + pb[j] * q[..., j - 1] + pd[j] * q[..., j]
+                (aO if odd else aE)[n] = (aO if odd else aE)[n] + pan
+        if not odd:
+            I = [aE[0], aE[1]]
+        else:
+            I = [0.5 * (aE[n] + pt[j] * (q[..., j - 1] + q[..., j])) + 0.5 * (T0[n] + aO[n])
+                 for n, q in enumerate((f, g))]
+        psi[..., j] = -2.0 * (I[1] - cotk[j] * I[0])
+    return psi
+
+
 class Generator(object):
     """Manage random field generation for a specified geometry (generate.py:21-142).
 
@@ -230,9 +293,27 @@ class Generator(object):
         return field
 
     def calculate_lensing_potential(self, i_min=None, show_plot=False, save_plot_name=None):
-        """generate.py:353-418 is outside the accelerated path."""
-        raise NotImplementedError(
-            'calculate_lensing_potential is not part of the B200 field-synthesis path yet.')
+        """Lensing potential psi(r) (generate.py:353-418): for every slice the Simpson integral
+        over comoving distance of -2 (cotK(D) - cotK(D_src)) dPhi, truncated below DC[i_min]
+        (default nz // 32).  Runs in place on the device field, which normally holds the
+        light-cone Newtonian potential (call calculate_newtonian_potential first); the returned
+        array is the host view of that buffer, as for the other results."""
+        nDC = self.DC.size
+        if i_min is None:
+            i_min = nDC // 32
+        if i_min < 0 or i_min >= nDC:
+            raise ValueError(
+                'Invalid i_min {}. Expected 0 - {}.'.format(i_min, nDC - 1))
+        if self._field_kind is None:
+            raise RuntimeError('No field to integrate: generate a potential first.')
+        self._engine.lensing(i_min, lensing_tables(self.DC, cot_k(self.DC, self.DA, self.cosmology.Ok0)))
+        self._field_kind = 'lensing'
+        field = self._host_field()
+        if show_plot or save_plot_name is not None:
+            self.plot_slice(field=field, clip_percent=15.0, clip_symmetric=True, show_plot=show_plot,
+                            save_plot_name=save_plot_name,
+                            label='Lensing potential $\\psi(r)$ [(Mpc/h) s$^{-2}$]')
+        return field
 
     def plot_slice(self, *args, **kwargs):
         """generate.py:420-516 needs matplotlib, which is not installed on the GPU box."""

@@ -238,3 +238,26 @@ def test_power_spectrum_recovered(lib):
         worst = max(worst, dev)
     assert worst < 5.0, worst
     assert abs(r.mean() - 1.0) < 5.0 / np.sqrt(r.size)
+
+
+# ------------------------------------------------------------------------------------------
+# lensing potential scan vs the reference loop (oracle, unpinned)
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape,dtype,i_min", [((16, 12, 64), np.float32, None), ((8, 8, 256), np.float32, 3),
+                                               ((8, 8, 256), np.float64, 0), ((12, 10, 8), np.float32, 1),
+                                               ((4, 6, 1024), np.float32, 32), ((4, 4, 4096), np.float32, None)])
+def test_lensing_potential_matches_reference_loop(lib, shape, dtype, i_min):
+    import randomfield_b200 as rf
+    gen = rf.Generator(*shape, 2.0, dtype=dtype)
+    gen.generate_delta_field(seed=11, save_potential=True)
+    dphi = gen.calculate_newtonian_potential(light_cone=True).copy()
+    psi = gen.calculate_lensing_potential(i_min=i_min).copy()
+    ref = oracle.lensing_potential(dphi, gen.DC, gen.DA, Ok0=gen.cosmology.Ok0, i_min=i_min)
+    assert psi.shape == shape and psi.dtype == dtype
+    im = shape[2] // 32 if i_min is None else i_min
+    assert np.all(psi[:, :, :im] == 0)
+    scale = np.abs(ref.astype(np.float64)).max()
+    err = np.abs(psi.astype(np.float64) - ref.astype(np.float64)).max() / scale
+    assert err <= (2e-6 if dtype == np.float32 else 1e-12), err
+    with pytest.raises(ValueError):
+        gen.calculate_lensing_potential(i_min=shape[2])

@@ -131,3 +131,41 @@ def test_all_to_all_gloo_world2():
         out = mgr.dict()
         mp.spawn(_gloo_worker, args=(world, port, (8, 12, 8), out), nprocs=world, join=True)
         assert dict(out) == {0: True, 1: True}
+
+
+# ------------------------------------------------------------------------------------------
+# lensing potential: oracle restatement and the O(nz) scan form
+# ------------------------------------------------------------------------------------------
+def test_simps_old_matches_simpson_for_odd_counts_and_avg_rule_for_even():
+    import scipy.integrate
+    rng = np.random.RandomState(3)
+    x = np.cumsum(rng.uniform(0.5, 2.0, size=21))
+    y = rng.normal(size=(3, 21))
+    # odd sample count: plain composite Simpson on non-uniform abscissae (any scipy)
+    assert np.allclose(oracle.simps_old(y, x), scipy.integrate.simpson(y, x=x), rtol=0, atol=1e-13)
+    # even count: average of (Simpson on first N-1 + last trapezoid) and (first trapezoid + Simpson on last N-1)
+    n = 10
+    first = oracle.simps_old(y[..., :n - 1], x[:n - 1]) + 0.5 * (x[n - 1] - x[n - 2]) * (y[..., n - 1] + y[..., n - 2])
+    last = oracle.simps_old(y[..., 1:n], x[1:n]) + 0.5 * (x[1] - x[0]) * (y[..., 0] + y[..., 1])
+    assert np.allclose(oracle.simps_old(y[..., :n], x[:n]), 0.5 * (first + last), rtol=0, atol=1e-14)
+    # exact for cubics on uniform abscissae with an odd count
+    xu = np.linspace(0.0, 2.0, 9)
+    assert abs(oracle.simps_old(xu ** 3, xu) - 4.0) < 1e-13
+
+
+@pytest.mark.parametrize("nz,i_min,ok0", [(32, 1, 0.0), (32, 0, 0.0), (33, 2, 0.05), (64, None, -0.02), (10, 3, 0.0)])
+def test_lensing_scan_form_equals_reference_loop(nz, i_min, ok0):
+    """The parity-split prefix-sum form the device kernel uses (generate.lensing_scan_host) equals
+    the reference's one-integral-per-slice loop (oracle.lensing_potential, generate.py:374-410)."""
+    from randomfield_b200.generate import cot_k, lensing_scan_host, lensing_tables
+    rng = np.random.RandomState(nz)
+    DC = np.arange(nz) * 2.0 if nz != 33 else np.cumsum(rng.uniform(1.0, 3.0, size=nz))
+    DA = DC * (1 + 0.01 * np.arange(nz))
+    dphi = rng.normal(size=(4, 3, nz))
+    ref = oracle.lensing_potential(dphi, DC, DA, Ok0=ok0, i_min=i_min)
+    im = nz // 32 if i_min is None else i_min
+    got = lensing_scan_host(dphi, lensing_tables(DC, cot_k(DC, DA, ok0)), im)
+    assert np.abs(got - ref).max() <= 1e-13 * np.abs(ref).max()
+    assert np.all(ref[..., :im] == 0)
+    with pytest.raises(ValueError):
+        oracle.lensing_potential(dphi, DC, DA, i_min=nz)
