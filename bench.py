@@ -49,7 +49,8 @@ def kernel_names(grid, pipelined):
     k1 = ("k1q_generate_xfft" if k1q else "k1p_generate_xfft") if grid[0] <= 1024 else (
         "k1b_generate_xfft" if big else PASS_NAMES[0])
     k2 = "k2p_strided_fft" if grid[1] <= 1024 else ("k2b_strided_fft" if big else PASS_NAMES[1])
-    return (k1, k2, "k3p_c2r_lines")
+    k3 = "k3q_c2r_lines" if (os.environ.get("RF_K3Q", "1") != "0" and grid[2] >= 128) else "k3p_c2r_lines"
+    return (k1, k2, k3)
 
 
 def measured_peaks():

@@ -43,6 +43,7 @@ struct rf_ctx {
   bool pipe = false;        // TMA-pipelined kernels (f32, env RF_PIPE != 0)
   bool fuse = false;        // fused y+z kernel k23p (env RF_FUSE != 0)
   bool k1q = true;          // pass 1 with two CTAs per SM (env RF_K1Q=0: one-CTA k1p)
+  bool k3q = true;          // pass 3 with the three-deep in-place ring (env RF_K3Q=0: k3p)
   bool fuse12 = false;      // passes 1 + 2 in one kernel when nx == ny in {512, 1024}, single GPU (env RF_FUSE12=1)
   bool pass2_done = false;  // set by the fused kernel: rf_finish_yz starts at pass 3
   int hinge_lo = 0, hinge_hi = -1;   // cells of the sigma table the grid's modes can touch
@@ -148,6 +149,8 @@ extern "C" int rf_create(int nx, int ny, int nz, int dtype, int rank, int world,
     const char* envq = getenv("RF_K1Q");
     c->k1q = !(envq && envq[0] == '0');
     // opt-in: measured slower than k1q + k2p on B200
+    const char* env3 = getenv("RF_K3Q");
+    c->k3q = !(env3 && env3[0] == '0');
     const char* env12 = getenv("RF_FUSE12");
     c->fuse12 = env12 && env12[0] == '1';
   }
@@ -981,7 +984,7 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
             q.partials = c->partials;
           }
           mark(c, 4);
-          e = PipeLaunch<NN>::k3p(q, grid, c->stream);
+          e = c->k3q ? PipeLaunch<NN>::k3q(q, grid, c->stream) : PipeLaunch<NN>::k3p(q, grid, c->stream);
           mark(c, 5);
         });
         c->launches++;

@@ -1,0 +1,244 @@
+// rf_k3q.cuh -- pass 3 (c2r along the contiguous axis) with a THREE-deep tile ring.
+//
+// k3p keeps two dense 64 KB buffers plus a 66 KB padded work buffer: while one tile is
+// transformed the other buffer has to drain its store AND receive the next load, so the FFT
+// warps wait for HBM latency about 40 % of the time (5.5 TB/s).  Here the transform of a tile
+// is in place in its own buffer -- step A: every thread reads its radix-R1 items, barrier,
+// writes the padded layout; step B: reads its radix-R2 items, barrier, writes the dense
+// layout -- so the work buffer goes away and three 66 KB buffers fit: one loading, one being
+// transformed, one draining, at all times.  Same arithmetic, in the same order, as k3p.
+#pragma once
+#include "rf_pipe.cuh"
+
+namespace rf {
+namespace pipe {
+
+template <int NZ>
+constexpr int k3q_smem_bytes() {
+  return 3 * LPlan<NZ>::kWorkBytes + kBarBytes;
+}
+
+// one tile, in place in `B` (dense [TL][H] at the start of a kWorkBytes buffer)
+template <int NZ>
+__device__ __forceinline__ void k3q_tile_body(cpx<float>* __restrict__ B, int tid,
+                                              const cpx<float> (&twr)[LPlan<NZ>::R1],
+                                              const cpx<float> (&twu)[K3Consts<NZ>::kPairsPerThread],
+                                              const float* zs, float& a1, float& a2, const cpx<float>* twH) {
+  using P = LPlan<NZ>;
+  constexpr int H = P::H, HE = P::HE, R1 = P::R1, R2 = HE / R1, M = P::M;
+  constexpr int kPairsPerThread = K3Consts<NZ>::kPairsPerThread;
+  using L = LayoutLinesPad<P::WP, P::M>;
+  constexpr int IA = M * P::TE / kConsumers, IB = R1 * P::TE / kConsumers;
+  static_assert(IA * kConsumers == M * P::TE && IB * kConsumers == R1 * P::TE, "items per thread");
+  static_assert(IA * R1 == 32 && IB * R2 == 32, "32 values per thread and step");
+  // ---- Hermitian unpack, in place (as k3_tile_body) ----
+  if constexpr (H / 2 >= kConsumers) {
+#pragma unroll 2
+    for (int l = 0; l < P::TL; ++l) {
+      cpx<float>* Lp = B + l * H;
+      sfor<0, kPairsPerThread>([&](auto qi) {
+        constexpr int q = decltype(qi)::value;
+        const int k = tid + q * kConsumers;
+        if (q == 0 && k == 0) {
+          cpx<float> a = Lp[0], m = Lp[H / 2];
+          Lp[0] = {a.x + a.y, a.x - a.y};
+          Lp[H / 2] = {2.f * m.x, -2.f * m.y};
+        } else {
+          cpx<float> a = Lp[k], c = Lp[H - k];
+          cpx<float> e = {a.x + c.x, a.y - c.y};
+          cpx<float> d = {a.x - c.x, a.y + c.y};
+          cpx<float> o = cmul(d, twu[q]);
+          Lp[k] = {e.x - o.y, e.y + o.x};
+          Lp[H - k] = {e.x + o.y, o.x - e.y};
+        }
+      });
+    }
+  } else {
+    constexpr int kLinesPerSweep = kConsumers / (H / 2);
+    const int k = tid % (H / 2);
+    for (int l = tid / (H / 2); l < P::TL; l += kLinesPerSweep) {
+      cpx<float>* Lp = B + l * H;
+      if (k == 0) {
+        cpx<float> a = Lp[0], m = Lp[H / 2];
+        Lp[0] = {a.x + a.y, a.x - a.y};
+        Lp[H / 2] = {2.f * m.x, -2.f * m.y};
+      } else {
+        cpx<float> a = Lp[k], c = Lp[H - k];
+        cpx<float> e = {a.x + c.x, a.y - c.y};
+        cpx<float> d = {a.x - c.x, a.y + c.y};
+        cpx<float> o = cmul(d, twu[0]);
+        Lp[k] = {e.x - o.y, e.y + o.x};
+        Lp[H - k] = {e.x + o.y, o.x - e.y};
+      }
+    }
+  }
+  ConsumerSync()();
+  if constexpr (P::SPLIT == 2) {
+    for (int w = tid; w < P::TL * (H / 2); w += kConsumers) {
+      const int l = w / (H / 2), k = w % (H / 2);
+      cpx<float>* Lp = B + l * H + k;
+      cpx<float> a = Lp[0], c = Lp[H / 2];
+      cpx<float> tw = ldg_cpx(twH + k);
+      Lp[0] = a + c;
+      Lp[H / 2] = cmul(a - c, tw);
+    }
+    ConsumerSync()();
+  }
+  // ---- step A: dense -> registers | barrier | registers -> padded ----
+  cpx<float> v[IA][R1];
+  sfor<0, IA>([&](auto qi) {
+    constexpr int q = decltype(qi)::value;
+    const int w = tid + q * kConsumers;
+    int j, l;
+    L::split(w, M, j, l);
+    const cpx<float>* Lp = B + l * HE + j;
+    sfor<0, R1>([&](auto mi) {
+      constexpr int m = decltype(mi)::value;
+      v[q][m] = ld_cpx(Lp + M * m);
+    });
+  });
+  ConsumerSync()();
+  sfor<0, IA>([&](auto qi) {
+    constexpr int q = decltype(qi)::value;
+    const int w = tid + q * kConsumers;
+    int j, l;
+    L::split(w, M, j, l);
+    fft_dif<R1, true>(v[q]);
+    cpx<float>* wp = B + L::idx2(0, j, l);
+    sfor<0, R1>([&](auto ki) {
+      constexpr int k1 = decltype(ki)::value;
+      cpx<float> x = v[q][brev<R1>(k1)];
+      if constexpr (k1 > 0) x = cmul(x, twr[k1]);
+      st_cpx(wp + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), x);
+    });
+  });
+  ConsumerSync()();
+  // ---- step B: padded -> registers | barrier | registers -> dense (+ statistics, z scale) ----
+  cpx<float> u[IB][R2];
+  sfor<0, IB>([&](auto qi) {
+    constexpr int q = decltype(qi)::value;
+    const int w = tid + q * kConsumers;
+    int k1, l;
+    L::split(w, R1, k1, l);
+    const cpx<float>* wp = B + L::idx2(k1, 0, l);
+    sfor<0, R2>([&](auto ji) {
+      constexpr int j = decltype(ji)::value;
+      u[q][j] = ld_cpx(wp + (L::idx2(0, j, 0) - L::idx2(0, 0, 0)));
+    });
+  });
+  ConsumerSync()();
+  sfor<0, IB>([&](auto qi) {
+    constexpr int q = decltype(qi)::value;
+    const int w = tid + q * kConsumers;
+    int k1, l;
+    L::split(w, R1, k1, l);
+    fft_dif<R2, true>(u[q]);
+    sfor<0, R2>([&](auto ki) {
+      constexpr int k2 = decltype(ki)::value;
+      cpx<float> x = u[q][brev<R2>(k2)];
+      const int k = k1 + R1 * k2;
+      a1 += x.x + x.y;
+      a2 = fmaf(x.x, x.x, fmaf(x.y, x.y, a2));
+      const int pos = P::SPLIT == 1 ? k : P::SPLIT * k + (l % P::SPLIT);
+      const int line = l / P::SPLIT;
+      if (zs) {
+        float2 z = __ldg(reinterpret_cast<const float2*>(zs) + pos);
+        x.x *= z.x;
+        x.y *= z.y;
+      }
+      st_cpx(B + line * H + pos, x);
+    });
+  });
+}
+
+template <int NZ>
+__global__ void __launch_bounds__(kThreads, 1) k3q_c2r_lines(const K3PParams p) {
+  using P = LPlan<NZ>;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  constexpr int kBufElems = P::kWorkBytes / 8;
+  static_assert(P::kWorkBytes % 128 == 0, "bulk copies need 16-byte aligned buffers");
+  cpx<float>* const buf0 = reinterpret_cast<cpx<float>*>(smem_raw);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + 3 * P::kWorkBytes);
+  uint64_t* full = bars;       // [3] tile landed
+  uint64_t* done = bars + 3;   // [3] FFT warps finished the tile
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    for (int b = 0; b < 3; ++b) {
+      mbar_init(&full[b], 1);
+      mbar_init(&done[b], kConsumers);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  const int first = blockIdx.x, step = gridDim.x;
+  char* gbase = reinterpret_cast<char*>(p.buf) + (size_t)p.tile0 * P::kDenseBytes;
+  constexpr size_t kTile = P::kDenseBytes;
+
+  if (tid >= kConsumers) {
+    if (tid == kConsumers) {
+      int n = 0;
+      for (int t = first; t < p.ntiles && n < 3; t += step, ++n) {
+        mbar_expect_tx(&full[n], (uint32_t)kTile);
+        bulk_g2s(buf0 + n * kBufElems, gbase + (size_t)t * kTile, (uint32_t)kTile, &full[n]);
+      }
+      int i = 0, b = 0, ph = 0;
+      for (int t = first; t < p.ntiles; t += step, ++i) {
+        // while the FFT warps work on tile i: wait for the store of tile i-1 to be read out
+        // of its buffer and refill that buffer with tile i+2 (two tile times ahead of its use)
+        if (i >= 1) {
+          const int pb = b == 0 ? 2 : b - 1;
+          const int t3 = t + 2 * step;
+          if (t3 < p.ntiles) {
+            bulk_wait_read0();
+            mbar_expect_tx(&full[pb], (uint32_t)kTile);
+            bulk_g2s(buf0 + pb * kBufElems, gbase + (size_t)t3 * kTile, (uint32_t)kTile, &full[pb]);
+          }
+        }
+        mbar_wait(&done[b], ph);
+        bulk_s2g(gbase + (size_t)t * kTile, buf0 + b * kBufElems, (uint32_t)kTile);
+        bulk_commit();
+        if (++b == 3) { b = 0; ph ^= 1; }
+      }
+      bulk_wait0();
+    }
+    return;
+  }
+
+  double s1 = 0.0, s2 = 0.0;
+  const float* zs = p.zscale;
+  cpx<float> twr[P::R1];
+  cpx<float> twu[K3Consts<NZ>::kPairsPerThread];
+  k3_load_twiddles<NZ>(twr, twu, p.twH, p.twN, tid);
+  int b = 0, ph = 0;
+  for (int t = first; t < p.ntiles; t += step) {
+    cpx<float>* const B = buf0 + b * kBufElems;
+    mbar_wait(&full[b], ph);
+    float a1 = 0.f, a2 = 0.f;
+    k3q_tile_body<NZ>(B, tid, twr, twu, zs, a1, a2, p.twH);
+    s1 += (double)a1;
+    s2 += (double)a2;
+    fence_proxy_async();
+    mbar_arrive(&done[b]);
+    if (++b == 3) { b = 0; ph ^= 1; }
+  }
+  if (p.partials) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    __shared__ double red[2][kConsumers / 32];
+    const int wid = tid >> 5, lane = tid & 31;
+    if (lane == 0) { red[0][wid] = s1; red[1][wid] = s2; }
+    ConsumerSync()();
+    if (tid == 0) {
+      double t1 = 0, t2 = 0;
+      for (int q = 0; q < kConsumers / 32; ++q) { t1 += red[0][q]; t2 += red[1][q]; }
+      p.partials[2 * (size_t)blockIdx.x] = t1;
+      p.partials[2 * (size_t)blockIdx.x + 1] = t2;
+    }
+  }
+}
+
+}  // namespace pipe
+}  // namespace rf

@@ -6,6 +6,7 @@
 #include "rf_pipe.cuh"
 #include "rf_big.cuh"
 #include "rf_fuse12.cuh"
+#include "rf_k3q.cuh"
 
 namespace rf {
 
@@ -23,6 +24,7 @@ template <int N>
 struct PipeLaunch {
   static int k3p(const pipe::K3PParams& p, int grid, cudaStream_t s);
   static int k3p_lines_per_tile();
+  static int k3q(const pipe::K3PParams& p, int grid, cudaStream_t s);   // three-deep ring, in-place tiles
   // N <= 1024: rf_pipe.cuh kernels; N = 2048, 4096: the single-buffer kernels of rf_big.cuh
   static int k2p(const CUtensorMap& in, const CUtensorMap& out, const pipe::K2PParams& p, int grid,
                  cudaStream_t s);

@@ -24,6 +24,18 @@ int PipeLaunch<N>::k3p(const pipe::K3PParams& p, int grid, cudaStream_t s) {
   return (int)cudaGetLastError();
 }
 template <>
+int PipeLaunch<N>::k3q(const pipe::K3PParams& p, int grid, cudaStream_t s) {
+  constexpr int smem = pipe::k3q_smem_bytes<N>();
+  if constexpr (smem <= 227 * 1024) {
+    int e;
+    if ((e = set_smem_pipe(pipe::k3q_c2r_lines<N>, smem))) return e;
+    pipe::k3q_c2r_lines<N><<<grid, pipe::kThreads, smem, s>>>(p);
+    return (int)cudaGetLastError();
+  } else {
+    return k3p(p, grid, s);   // short lines: the padded buffers of three tiles do not fit
+  }
+}
+template <>
 int PipeLaunch<N>::k3p_lines_per_tile() {
   return pipe::LPlan<N>::TL;
 }
