@@ -57,6 +57,7 @@ struct rf_ctx {
   // [G][nxl][nyl][wc] while pass 1 of chunk c+1 and pass 2 of chunk c-1 run on the SMs
   int ck_n = 0;             // chunks (0: off)
   int ck_cur = -1;          // chunk the next pass-1 / pass-2 launch works on (-1: whole field)
+  int ck_reserve = 0;       // SMs left out of the chunk launches' grids (world > 1; env RF_RESERVE_SMS)
   void* send = nullptr;     // [ck_n][nx][nyl][wc]
   cudaStream_t comm = nullptr;
   cudaEvent_t ev_k1 = nullptr, ev_x = nullptr, ev_s = nullptr;
@@ -672,19 +673,28 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
         // one chunk of columns into its contiguous block of the send buffer
         const int wc = nzc / c->ck_n;
         q.z_base = c->ck_cur * wc;
-        q.nxl = c->nx;
-        char* base = (char*)c->send + (size_t)c->ck_cur * c->nx * c->nyl * wc * sizeof(cpx<float>);
+        q.nxl = c->nxl;
+        // one store map per destination block [nxl][nyl][wc]: blocks of the other ranks go to the
+        // send buffer (the copy engines push them), this rank's own block goes straight into its
+        // receive buffer -- no local copy
+        const size_t block = (size_t)c->nxl * c->nyl * wc * sizeof(cpx<float>);
+        const size_t chunk_off = (size_t)c->ck_cur * c->world * block;
         RF_DISPATCH_PIPE(c->nx, {
           const int tz = PipeLaunch<NN>::tile_cols();
           q.ztiles = wc / tz;
           q.ntiles = c->nyl * q.ztiles;
           uint64_t sout[2] = {(uint64_t)wc * 8, (uint64_t)c->nyl * wc * 8};
-          uint64_t dout[3] = {(uint64_t)2 * wc, (uint64_t)c->nyl, (uint64_t)c->nx};
-          uint32_t bout[3] = {(uint32_t)2 * tz, 1, (uint32_t)PipeLaunch<NN>::box_rows()};
-          int e2 = make_tensor_map(&mout.m[0], base, 3, dout, sout, bout);
-          if (e2) return e2;
+          uint64_t dout[3] = {(uint64_t)2 * wc, (uint64_t)c->nyl, (uint64_t)c->nxl};
+          uint32_t bout[3] = {(uint32_t)2 * tz, 1, (uint32_t)std::min(PipeLaunch<NN>::box_rows(), c->nxl)};
+          for (int d = 0; d < c->world; ++d) {
+            char* base = (c->world > 1 && d == c->rank ? (char*)c->recv : (char*)c->send) + chunk_off + (size_t)d * block;
+            int e2 = make_tensor_map(&mout.m[d], base, 3, dout, sout, bout);
+            if (e2) return e2;
+          }
           const bool twocta = c->k1q && PipeLaunch<NN>::k1q_fits(c->lut_n);
-          int grid = std::min(q.ntiles, (twocta ? 2 : PipeLaunch<NN>::ctas_per_sm()) * c->num_sms);
+          // a few SMs stay free so that the 1-CTA fence collectives between chunks start at once
+          // instead of waiting for a persistent grid to drain
+          int grid = std::min(q.ntiles, (twocta ? 2 : PipeLaunch<NN>::ctas_per_sm()) * (c->num_sms - c->ck_reserve));
           e = twocta ? PipeLaunch<NN>::k1q(c->noise != nullptr, potential != 0, mout, q, grid, c->stream)
                      : PipeLaunch<NN>::k1p(c->noise != nullptr, potential != 0, mout, q, grid, c->stream);
         });
@@ -1117,6 +1127,8 @@ extern "C" int rf_chunk_config(rf_ctx* c, int nchunks) {
   if (!c->ev_s) RF_CUDA(cudaEventCreateWithFlags(&c->ev_s, cudaEventDisableTiming));
   c->ck_n = nchunks;
   c->ck_cur = -1;
+  c->ck_reserve = 0;   // measured: no gain from keeping SMs free for the fence collectives
+  if (const char* er = getenv("RF_RESERVE_SMS")) c->ck_reserve = std::min(std::max(0, atoi(er)), c->num_sms / 2);
   return RF_OK;
 }
 
@@ -1160,7 +1172,7 @@ extern "C" int rf_chunk_exchange(rf_ctx* c, int chunk) {
   const size_t wc = (size_t)(c->nz / 2) / c->ck_n;
   const size_t block = (size_t)c->nxl * c->nyl * wc * sizeof(cpx<float>);
   const size_t chunk_off = (size_t)chunk * c->world * block;
-  for (int i = 0; i < c->world; ++i) {
+  for (int i = 0; i + 1 < c->world; ++i) {        // (the own block was stored in place by pass 1)
     const int d = (c->rank + 1 + i) % c->world;   // staggered: no receiver is everybody's first target
     char* peer = (char*)(c->peer_recv[d] ? c->peer_recv[d] : (d == c->rank ? c->recv : nullptr));
     if (!peer) return fail(RF_ERR_STATE, "rf_chunk_exchange: receive buffer of a peer is not mapped");
@@ -1224,7 +1236,7 @@ extern "C" int rf_chunk_pass2(rf_ctx* c, int chunk) {
     uint32_t bout[3] = {(uint32_t)2 * tz, (uint32_t)PipeLaunch<NN>::box_rows(), 1};
     e2 = make_tensor_map(&mout, c->field, 3, dout, sout, bout);
     if (e2) return e2;
-    const int grid = std::min(q.ntiles, PipeLaunch<NN>::ctas_per_sm() * c->num_sms);
+    const int grid = std::min(q.ntiles, PipeLaunch<NN>::ctas_per_sm() * (c->num_sms - c->ck_reserve));
     const bool tm = c->timing && (int)c->ck_ev.size() == 4 * c->ck_n;
     if (tm) cudaEventRecord(c->ck_ev[(c->ck_n + chunk) * 2], c->stream);
     e = PipeLaunch<NN>::k2p(min, mout, q, grid, c->stream);
