@@ -38,9 +38,12 @@ struct BPlan;
 #ifndef RF_BIG2048_TZ
 #define RF_BIG2048_TZ 8
 #endif
+#ifndef RF_BIG2048_NT
+#define RF_BIG2048_NT (64 * RF_BIG2048_TZ)
+#endif
 template <>
 struct BPlan<2048> {
-  static constexpr int R1 = 16, R2 = 16, R3 = 8, TZ = RF_BIG2048_TZ, NT = 64 * RF_BIG2048_TZ,
+  static constexpr int R1 = 16, R2 = 16, R3 = 8, TZ = RF_BIG2048_TZ, NT = RF_BIG2048_NT,
                        CTAS = 8 / RF_BIG2048_TZ;
 };
 // plans of the pass-2 warp group of the fused kernel (rf_fuse12.cuh): 256 threads, 64 KB tiles
