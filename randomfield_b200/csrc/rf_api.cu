@@ -1326,6 +1326,28 @@ static int lensing_impl(rf_ctx* c, int i_min, const double* tables5) {
   LensTables tb;
   tb.cotk = c->lens_dev; tb.pa = c->lens_dev + nz; tb.pb = c->lens_dev + 2 * nz;
   tb.pd = c->lens_dev + 3 * nz; tb.pt = c->lens_dev + 4 * nz;
+  const long long nlines4 = (long long)c->nxl * c->ny;
+  const char* el4 = getenv("RF_LENS4");
+  const bool lens4 = !(el4 && el4[0] == '0');
+  constexpr int S8 = LensS<T>::value;
+  auto go = [&](auto kern, int S, int tpb) {
+    const int per_sm = std::max(1, (sizeof(T) == 4 && S == 4 ? 768 : 512) / tpb);
+    const int lpc = tpb / (nz / S);
+    const int grid = (int)std::min<long long>((nlines4 + lpc - 1) / lpc, (long long)c->num_sms * per_sm);
+    kern<<<grid, tpb, 0, c->stream>>>((T*)c->field, nlines4, nz, i_min, tb);
+    c->launches++;
+    c->stats_valid = false;
+    return cudaGetLastError();
+  };
+  // fixed sample ownership: coefficients in registers, 16-byte vectors per thread and line
+  if (lens4 && lens4_supported(nz, S8)) {
+    RF_CUDA(nz / S8 <= 256 ? go(lensing_scan4_kernel<T, 256, S8>, S8, 256) : go(lensing_scan4_kernel<T, 512, S8>, S8, 512));
+    return RF_OK;
+  }
+  if (lens4 && S8 != 4 && lens4_supported(nz, 4)) {
+    RF_CUDA(nz / 4 <= 256 ? go(lensing_scan4_kernel<T, 256, 4>, 4, 256) : go(lensing_scan4_kernel<T, 512, 4>, 4, 512));
+    return RF_OK;
+  }
   int warps = 16;
   while (warps > 1 && lens_smem_bytes(nz, warps, sizeof(T)) > 112 * 1024) warps >>= 1;
   const size_t smem = lens_smem_bytes(nz, warps, sizeof(T));

@@ -245,7 +245,10 @@ def test_power_spectrum_recovered(lib):
 # ------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("shape,dtype,i_min", [((16, 12, 64), np.float32, None), ((8, 8, 256), np.float32, 3),
                                                ((8, 8, 256), np.float64, 0), ((12, 10, 8), np.float32, 1),
-                                               ((4, 6, 1024), np.float32, 32), ((4, 4, 4096), np.float32, None)])
+                                               ((4, 6, 1024), np.float32, 32), ((4, 4, 4096), np.float32, None),
+                                               ((6, 4, 128), np.float32, 5), ((4, 6, 384), np.float32, 2),
+                                               ((4, 4, 2048), np.float32, None), ((6, 4, 512), np.float64, 7),
+                                               ((40, 34, 256), np.float32, 0), ((2, 2, 4096), np.float64, 100)])
 def test_lensing_potential_matches_reference_loop(lib, shape, dtype, i_min):
     import randomfield_b200 as rf
     gen = rf.Generator(*shape, 2.0, dtype=dtype)
