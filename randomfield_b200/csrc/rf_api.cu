@@ -1340,12 +1340,21 @@ static int lensing_impl(rf_ctx* c, int i_min, const double* tables5) {
     return cudaGetLastError();
   };
   // fixed sample ownership: coefficients in registers, 16-byte vectors per thread and line
+  // one line group per CTA where a line takes 128 threads or more (the per-line barrier then
+  // spans as few warps as possible), several lines per 128-thread CTA below that
+  auto pick = [&](auto s_tag) {
+    constexpr int S = decltype(s_tag)::value;
+    const int G = nz / S;
+    return G <= 128 ? go(lensing_scan4_kernel<T, 128, S>, S, 128)
+         : G <= 256 ? go(lensing_scan4_kernel<T, 256, S>, S, 256)
+                    : go(lensing_scan4_kernel<T, 512, S>, S, 512);
+  };
   if (lens4 && lens4_supported(nz, S8)) {
-    RF_CUDA(nz / S8 <= 256 ? go(lensing_scan4_kernel<T, 256, S8>, S8, 256) : go(lensing_scan4_kernel<T, 512, S8>, S8, 512));
+    RF_CUDA(pick(std::integral_constant<int, S8>()));
     return RF_OK;
   }
   if (lens4 && S8 != 4 && lens4_supported(nz, 4)) {
-    RF_CUDA(nz / 4 <= 256 ? go(lensing_scan4_kernel<T, 256, 4>, 4, 256) : go(lensing_scan4_kernel<T, 512, 4>, 4, 512));
+    RF_CUDA(pick(std::integral_constant<int, 4>()));
     return RF_OK;
   }
   int warps = 16;
