@@ -285,6 +285,18 @@ def run_ours(args):
             traffic = tj["dram_bytes_per_launch"].get(names[dom])
     except Exception:
         pass
+    issue = None
+    try:   # the dominant kernel of 1024^3 is issue-bound: say how close to the issue-slot ceiling it runs
+        winst = tj["warp_inst_per_launch"].get(names[dom]) if traffic is not None else None
+        if winst:
+            sms = torch.cuda.get_device_properties(0).multi_processor_count
+            mhz = (clocks or {}).get("sm_mhz") or 1965.0
+            ipeak = sms * 4 * mhz * 1e6          # 4 warp schedulers per SM, one instruction per clock each
+            issue = {"warp_inst_per_launch": winst, "achieved_Ginst_s": winst / (pass_ms[dom] * 1e-3) / 1e9,
+                     "peak_Ginst_s": ipeak / 1e9, "frac": winst / (pass_ms[dom] * 1e-3) / ipeak,
+                     "source": "smsp__inst_executed.sum of the committed ncu capture"}
+    except Exception:
+        issue = None
     dom_bytes = PASS_BYTES_PER_CELL[dom] * local_cells
     achieved = dom_bytes / (pass_ms[dom] * 1e-3) / 1e9
     step_achieved = BYTES_PER_CELL * local_cells / (ms_step * 1e-3) / 1e9
@@ -303,7 +315,7 @@ def run_ours(args):
         "roofline": {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": dom_bytes},
+                     "algorithmic_bytes_per_launch": dom_bytes, "issue_slots": issue},
         "roofline_step": {"bytes_per_cell": BYTES_PER_CELL, "achieved": step_achieved, "peak": peak,
                           "unit": "GB/s", "frac": step_achieved / peak,
                           "frac_of_8TBs": step_achieved / 8000.0},

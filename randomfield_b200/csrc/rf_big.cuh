@@ -60,6 +60,12 @@ struct BPlan<4096> {
   static constexpr int R1 = 16, R2 = 16, R3 = 16, TZ = 4, NT = 512, CTAS = 1;
 };
 
+#ifndef RF_K2B_AUXM_2048
+#define RF_K2B_AUXM_2048 (RF_BIG2048_TZ == 8 ? 10 : 6)
+#endif
+#ifndef RF_K2B_AUXM_4096
+#define RF_K2B_AUXM_4096 8
+#endif
 template <int N>
 struct BGeom {
   using P = BPlan<N>;
@@ -81,7 +87,7 @@ struct BGeom {
   static constexpr int kTwA = N, kTwB = M2 * (R2 + 1);
   static constexpr int kTwBytes = (kTwA + kTwB) * 8;
   // k2b: row blocks [0, kAuxM) of the next tile are prefetched into an auxiliary buffer
-  static constexpr int kAuxM = (N == 2048 && TZ == 8) ? 8 : 6;
+  static constexpr int kAuxM = N == 2048 ? RF_K2B_AUXM_2048 : N == 4096 ? RF_K2B_AUXM_4096 : 6;
   static constexpr int kAuxBytes = kAuxM * M * TZ * 8;
 };
 
