@@ -171,6 +171,25 @@ int rf_chunk_xpass(rf_ctx* ctx, uint64_t seed, int potential, int chunk);
 int rf_chunk_exchange(rf_ctx* ctx, int chunk);
 int rf_chunk_arrived(rf_ctx* ctx, int chunk);
 int rf_chunk_pass2(rf_ctx* ctx, int chunk);
+/* Split schedule for transfer-bound decompositions (world >= 4): pass 3 needs every chunk of
+ * a line, so with the plan above it cannot start before the LAST chunk has crossed NVLink.
+ * Here the exchange is also cut along the destination's local x axis: while pass 1 runs, only
+ * rows x in [0, xa) of every chunk are pushed (and pass 2 + pass 3 of those rows follow as soon
+ * as pass 1 is over); the remaining rows travel afterwards in x ranges [x0, x1), all chunks of
+ * a range in one pitched copy per peer, and pass 2 + pass 3 of one range overlap the transfer of
+ * the next.  Call order per step (every rank):
+ *   rf_chunk_begin_step; [fence]
+ *   for c: rf_chunk_xpass(c); rf_chunk_exchange_x(c, 0, xa, 1); [fence]; rf_chunk_arrived(c);
+ *          rf_chunk_pass2_x(c-1, 0, xa, c-1)
+ *   rf_chunk_pass2_x(last, 0, xa, last)
+ *   for every range s: rf_chunk_exchange_x(-1, x0, x1, 0); [fence]; rf_chunk_arrived(nchunks + s)
+ *   rf_chunk_pass3_x(0, xa, ..., last = 0)
+ *   for every range s: for c: rf_chunk_pass2_x(c, x0, x1, c == 0 ? nchunks + s : -1);
+ *                      rf_chunk_pass3_x(x0, x1, ..., last = (s is the final range))
+ * Same kernels on the same data as the plain chunked plan: the field is bit-identical. */
+int rf_chunk_exchange_x(rf_ctx* ctx, int chunk /* -1: every chunk */, int x0, int x1, int wait_pass1);
+int rf_chunk_pass2_x(rf_ctx* ctx, int chunk, int x0, int x1, int wait_index /* of rf_chunk_arrived, -1: none */);
+int rf_chunk_pass3_x(rf_ctx* ctx, int x0, int x1, const double* zscale, int want_stats, int last);
 
 /* raw device pointers for zero-copy wrapping (torch / DLPack) and for the all-to-all */
 void* rf_device_ptr(rf_ctx* ctx, int which);

@@ -63,6 +63,9 @@ SIGNATURES = {
     "rf_chunk_exchange": (_c.c_int, [_P, _c.c_int]),
     "rf_chunk_arrived": (_c.c_int, [_P, _c.c_int]),
     "rf_chunk_pass2": (_c.c_int, [_P, _c.c_int]),
+    "rf_chunk_exchange_x": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_int, _c.c_int]),
+    "rf_chunk_pass2_x": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_int, _c.c_int]),
+    "rf_chunk_pass3_x": (_c.c_int, [_P, _c.c_int, _c.c_int, _P, _c.c_int, _c.c_int]),
     "rf_is_fast": (_c.c_int, [_P]),
     "rf_is_pipelined": (_c.c_int, [_P]),
     "rf_launch_count": (_c.c_longlong, [_P]),
@@ -291,6 +294,18 @@ class Engine:
 
     def chunk_pass2(self, chunk):
         check(lib().rf_chunk_pass2(self._ctx, int(chunk)))
+
+    # split schedule: the exchange also cut along the destination's local x axis
+    def chunk_exchange_x(self, chunk, x0, x1, wait_pass1):
+        check(lib().rf_chunk_exchange_x(self._ctx, int(chunk), int(x0), int(x1), int(bool(wait_pass1))))
+
+    def chunk_pass2_x(self, chunk, x0, x1, wait_index=-1):
+        check(lib().rf_chunk_pass2_x(self._ctx, int(chunk), int(x0), int(x1), int(wait_index)))
+
+    def chunk_pass3_x(self, x0, x1, zscale=None, want_stats=True, last=False):
+        zs = None if zscale is None else np.ascontiguousarray(zscale, dtype=np.float64)
+        check(lib().rf_chunk_pass3_x(self._ctx, int(x0), int(x1), None if zs is None else ptr(zs),
+                                     int(bool(want_stats)), int(bool(last))))
 
     @property
     def is_fast(self):

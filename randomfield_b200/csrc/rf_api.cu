@@ -62,7 +62,12 @@ struct rf_ctx {
   cudaStream_t comm = nullptr;
   cudaEvent_t ev_k1 = nullptr, ev_x = nullptr, ev_s = nullptr;
   std::vector<cudaEvent_t> ev_xc;   // per chunk: exchange complete (recorded on the comm stream)
-  std::vector<cudaEvent_t> ck_ev;   // timing: [pass 1 | pass 2][chunk][start, stop]
+  // timing of a chunked step: one (start, stop, pass) record per launch, reused every step
+  std::vector<cudaEvent_t> seg_a, seg_b;
+  std::vector<int> seg_pass;
+  int seg_used = 0;
+  long long part_used = 0;          // statistics partials written by this step's pass-3 launches
+  bool zs_loaded = false;           // this step's z-scale table is on the device
   bool last_chunked = false;        // the last step ran through rf_chunk_*
   int num_sms = 148;
   size_t esize = 4;         // sizeof(T)
@@ -191,7 +196,8 @@ extern "C" int rf_destroy(rf_ctx* c) {
   for (void* p : ptrs)
     if (p) cudaFree(p);
   if (c->send) cudaFree(c->send);
-  for (cudaEvent_t ev : c->ck_ev) cudaEventDestroy(ev);
+  for (cudaEvent_t ev : c->seg_a) cudaEventDestroy(ev);
+  for (cudaEvent_t ev : c->seg_b) cudaEventDestroy(ev);
   for (cudaEvent_t ev : c->ev_xc) cudaEventDestroy(ev);
   if (c->comm) cudaStreamDestroy(c->comm);
   for (cudaEvent_t e : {c->ev_k1, c->ev_x, c->ev_s})
@@ -234,15 +240,13 @@ extern "C" int rf_get_timing(rf_ctx* c, double* a, double* b, double* d) {
   if (!c || !c->timing || !c->fast) return fail(RF_ERR_STATE, "rf_get_timing: timing is off or generic path");
   RF_CUDA(cudaStreamSynchronize(c->stream));
   float t[3] = {0, 0, 0};
-  if (c->last_chunked && (int)c->ck_ev.size() == 4 * c->ck_n) {
-    // chunked step: passes 1 and 2 are interleaved; report the sum of their chunk launches
-    for (int ps = 0; ps < 2; ++ps)
-      for (int k = 0; k < c->ck_n; ++k) {
-        float dt = 0;
-        RF_CUDA(cudaEventElapsedTime(&dt, c->ck_ev[(ps * c->ck_n + k) * 2], c->ck_ev[(ps * c->ck_n + k) * 2 + 1]));
-        t[ps] += dt;
-      }
-    RF_CUDA(cudaEventElapsedTime(&t[2], c->ev[4], c->ev[5]));
+  if (c->last_chunked && c->seg_used > 0) {
+    // chunked step: the passes are interleaved; report the sum of each pass's launches
+    for (int k = 0; k < c->seg_used; ++k) {
+      float dt = 0;
+      RF_CUDA(cudaEventElapsedTime(&dt, c->seg_a[k], c->seg_b[k]));
+      t[c->seg_pass[k]] += dt;
+    }
   } else {
     for (int i = 0; i < 3; ++i) RF_CUDA(cudaEventElapsedTime(&t[i], c->ev[2 * i], c->ev[2 * i + 1]));
   }
@@ -1089,6 +1093,23 @@ extern "C" int rf_finish_yz(rf_ctx* c, const double* zscale, int want_stats) {
 // ------------------------------------------------------------------------------------------
 // chunked exchange: pass 1 / copy-engine exchange / pass 2 per chunk of packed z columns
 // ------------------------------------------------------------------------------------------
+// timing record of one launch of a chunked step (pass 0, 1 or 2); -1 when timing is off
+static int seg_begin(rf_ctx* c, int pass) {
+  if (!c->timing) return -1;
+  if (c->seg_used == (int)c->seg_a.size()) {
+    cudaEvent_t a = nullptr, b = nullptr;
+    if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) return -1;
+    c->seg_a.push_back(a); c->seg_b.push_back(b); c->seg_pass.push_back(pass);
+  }
+  const int k = c->seg_used++;
+  c->seg_pass[k] = pass;
+  cudaEventRecord(c->seg_a[k], c->stream);
+  return k;
+}
+static void seg_end(rf_ctx* c, int k) {
+  if (k >= 0) cudaEventRecord(c->seg_b[k], c->stream);
+}
+
 static int pipe_tile_cols(int n) {
   RF_DISPATCH_PIPE(n, { return PipeLaunch<NN>::tile_cols(); });
   return 0;
@@ -1140,58 +1161,69 @@ extern "C" int rf_chunk_begin_step(rf_ctx* c) {
   if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_begin_step: chunked path not configured");
   RF_CUDA(cudaEventRecord(c->ev_s, c->stream));
   RF_CUDA(cudaStreamWaitEvent(c->comm, c->ev_s, 0));
+  c->seg_used = 0;
+  c->part_used = 0;
+  c->zs_loaded = false;
   return RF_OK;
 }
 
 extern "C" int rf_chunk_xpass(rf_ctx* c, uint64_t seed, int potential, int chunk) {
   if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_xpass: chunked path not configured");
   if (chunk < 0 || chunk >= c->ck_n) return fail(RF_ERR_ARG, "rf_chunk_xpass: bad chunk");
-  if (c->timing && (int)c->ck_ev.size() != 4 * c->ck_n) {
-    for (cudaEvent_t ev : c->ck_ev) cudaEventDestroy(ev);
-    c->ck_ev.assign((size_t)4 * c->ck_n, nullptr);
-    for (auto& ev : c->ck_ev) RF_CUDA(cudaEventCreate(&ev));
-  }
-  const bool tm = c->timing && !c->ck_ev.empty();
   c->last_chunked = true;
   c->ck_cur = chunk;
-  if (tm) cudaEventRecord(c->ck_ev[chunk * 2], c->stream);
+  const int sg = seg_begin(c, 0);
   int e = xpass_impl<float>(c, seed, potential);
-  if (tm) cudaEventRecord(c->ck_ev[chunk * 2 + 1], c->stream);
+  seg_end(c, sg);
   c->ck_cur = -1;
   if (e) return e;
   RF_CUDA(cudaEventRecord(c->ev_k1, c->stream));
   return RF_OK;
 }
 
-// copy engines: block d of send[chunk] -> block `rank` of recv[chunk] on rank d (peer memory)
-extern "C" int rf_chunk_exchange(rf_ctx* c, int chunk) {
-  if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_exchange: chunked path not configured");
-  if (chunk < 0 || chunk >= c->ck_n) return fail(RF_ERR_ARG, "rf_chunk_exchange: bad chunk");
-  RF_CUDA(cudaStreamWaitEvent(c->comm, c->ev_k1, 0));
-  if (c->world == 1) return RF_OK;   // pass 2 reads the send buffer directly
+// copy engines: rows x in [x0, x1) of block d of send[chunk] -> block `rank` of recv[chunk] on
+// rank d (peer memory); chunk < 0: the same rows of every chunk in one pitched copy per peer
+static int chunk_exchange_impl(rf_ctx* c, int chunk, int x0, int x1, bool wait_k1) {
+  if (wait_k1) RF_CUDA(cudaStreamWaitEvent(c->comm, c->ev_k1, 0));
+  if (c->world == 1 || x1 <= x0) return RF_OK;   // (one rank: pass 2 reads the send buffer directly)
   const size_t wc = (size_t)(c->nz / 2) / c->ck_n;
-  const size_t block = (size_t)c->nxl * c->nyl * wc * sizeof(cpx<float>);
-  const size_t chunk_off = (size_t)chunk * c->world * block;
+  const size_t row = (size_t)c->nyl * wc * sizeof(cpx<float>);     // one x of one block
+  const size_t block = (size_t)c->nxl * row;
+  const size_t chunk_off = chunk < 0 ? 0 : (size_t)chunk * c->world * block;
   for (int i = 0; i + 1 < c->world; ++i) {        // (the own block was stored in place by pass 1)
     const int d = (c->rank + 1 + i) % c->world;   // staggered: no receiver is everybody's first target
     char* peer = (char*)(c->peer_recv[d] ? c->peer_recv[d] : (d == c->rank ? c->recv : nullptr));
     if (!peer) return fail(RF_ERR_STATE, "rf_chunk_exchange: receive buffer of a peer is not mapped");
-    RF_CUDA(cudaMemcpyAsync(peer + chunk_off + (size_t)c->rank * block,
-                            (const char*)c->send + chunk_off + (size_t)d * block, block,
-                            cudaMemcpyDeviceToDevice, c->comm));
+    char* dst = peer + chunk_off + (size_t)c->rank * block + (size_t)x0 * row;
+    const char* src = (const char*)c->send + chunk_off + (size_t)d * block + (size_t)x0 * row;
+    if (chunk >= 0)
+      RF_CUDA(cudaMemcpyAsync(dst, src, (size_t)(x1 - x0) * row, cudaMemcpyDeviceToDevice, c->comm));
+    else
+      RF_CUDA(cudaMemcpy2DAsync(dst, (size_t)c->world * block, src, (size_t)c->world * block,
+                                (size_t)(x1 - x0) * row, (size_t)c->ck_n, cudaMemcpyDeviceToDevice, c->comm));
   }
   return RF_OK;
+}
+extern "C" int rf_chunk_exchange(rf_ctx* c, int chunk) {
+  if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_exchange: chunked path not configured");
+  if (chunk < 0 || chunk >= c->ck_n) return fail(RF_ERR_ARG, "rf_chunk_exchange: bad chunk");
+  return chunk_exchange_impl(c, chunk, 0, c->nxl, true);
+}
+extern "C" int rf_chunk_exchange_x(rf_ctx* c, int chunk, int x0, int x1, int wait_pass1) {
+  if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_exchange_x: chunked path not configured");
+  if (chunk >= c->ck_n || x0 < 0 || x1 > c->nxl || x0 > x1) return fail(RF_ERR_ARG, "rf_chunk_exchange_x: bad range");
+  return chunk_exchange_impl(c, chunk, x0, x1, wait_pass1 != 0);
 }
 
 // call after the cross-rank fence for this chunk has been queued on the comm stream
 extern "C" int rf_chunk_arrived(rf_ctx* c, int chunk) {
   if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_arrived: chunked path not configured");
-  if (chunk < 0 || chunk >= c->ck_n) return fail(RF_ERR_ARG, "rf_chunk_arrived: bad chunk");
-  // one event per chunk: the compute stream only waits for it when pass 2 of this chunk is
-  // queued (rf_chunk_pass2), after pass 1 of the following chunks
-  if ((int)c->ev_xc.size() < c->ck_n) {
+  if (chunk < 0 || chunk >= 4096) return fail(RF_ERR_ARG, "rf_chunk_arrived: bad index");
+  // one event per chunk (indices >= the chunk count: per x range of the split schedule): the
+  // compute stream only waits for it when the pass 2 that needs it is queued
+  if ((int)c->ev_xc.size() <= chunk) {
     const size_t old = c->ev_xc.size();
-    c->ev_xc.resize(c->ck_n, nullptr);
+    c->ev_xc.resize((size_t)chunk + 1, nullptr);
     for (size_t k = old; k < c->ev_xc.size(); ++k)
       RF_CUDA(cudaEventCreateWithFlags(&c->ev_xc[k], cudaEventDisableTiming));
   }
@@ -1199,12 +1231,14 @@ extern "C" int rf_chunk_arrived(rf_ctx* c, int chunk) {
   return RF_OK;
 }
 
-extern "C" int rf_chunk_pass2(rf_ctx* c, int chunk) {
-  if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_pass2: chunked path not configured");
-  if (chunk < 0 || chunk >= c->ck_n) return fail(RF_ERR_ARG, "rf_chunk_pass2: bad chunk");
-  if (chunk >= (int)c->ev_xc.size() || !c->ev_xc[chunk])
-    return fail(RF_ERR_STATE, "rf_chunk_pass2: rf_chunk_arrived has not been called for this chunk");
-  RF_CUDA(cudaStreamWaitEvent(c->stream, c->ev_xc[chunk], 0));
+// pass 2 of rows x in [x0, x1) of one chunk; waits for event `ev` of rf_chunk_arrived first (ev >= 0)
+static int chunk_pass2_impl(rf_ctx* c, int chunk, int x0, int x1, int ev) {
+  if (ev >= 0) {
+    if (ev >= (int)c->ev_xc.size() || !c->ev_xc[ev])
+      return fail(RF_ERR_STATE, "rf_chunk_pass2: rf_chunk_arrived has not been called for this index");
+    RF_CUDA(cudaStreamWaitEvent(c->stream, c->ev_xc[ev], 0));
+  }
+  if (x1 <= x0) return RF_OK;
   const int nzc = c->nz / 2, wc = nzc / c->ck_n;
   pipe::K2PParams q;
   q.tw = (const cpx<float>*)c->tw_y;
@@ -1212,7 +1246,6 @@ extern "C" int rf_chunk_pass2(rf_ctx* c, int chunk) {
   q.out_outer = (long long)c->ny * nzc;
   q.out_row = nzc;
   q.z_out_base = chunk * wc;
-  q.tile0 = 0;
   const size_t chunk_elems = (size_t)c->nx * c->nyl * wc;
   const cpx<float>* in = (const cpx<float>*)(c->world > 1 ? c->recv : c->send) + (size_t)chunk * chunk_elems;
   q.rows_per_src = c->world > 1 ? c->nyl : c->ny;
@@ -1221,7 +1254,8 @@ extern "C" int rf_chunk_pass2(rf_ctx* c, int chunk) {
   RF_DISPATCH_PIPE(c->ny, {
     const int tz = PipeLaunch<NN>::tile_cols();
     q.ztiles = wc / tz;
-    q.ntiles = c->nxl * q.ztiles;
+    q.tile0 = x0 * q.ztiles;
+    q.ntiles = (x1 - x0) * q.ztiles;
     q.box_rows = std::min(PipeLaunch<NN>::box_rows(), q.rows_per_src);
     const int nsrc = c->ny / q.rows_per_src;
     // [src][nxl][rows_per_src][wc]; single GPU: [nx][ny][wc]
@@ -1237,14 +1271,87 @@ extern "C" int rf_chunk_pass2(rf_ctx* c, int chunk) {
     e2 = make_tensor_map(&mout, c->field, 3, dout, sout, bout);
     if (e2) return e2;
     const int grid = std::min(q.ntiles, PipeLaunch<NN>::ctas_per_sm() * (c->num_sms - c->ck_reserve));
-    const bool tm = c->timing && (int)c->ck_ev.size() == 4 * c->ck_n;
-    if (tm) cudaEventRecord(c->ck_ev[(c->ck_n + chunk) * 2], c->stream);
+    const int sg = seg_begin(c, 1);
     e = PipeLaunch<NN>::k2p(min, mout, q, grid, c->stream);
-    if (tm) cudaEventRecord(c->ck_ev[(c->ck_n + chunk) * 2 + 1], c->stream);
+    seg_end(c, sg);
   });
   c->launches++;
   RF_CUDA(e);
+  return RF_OK;
+}
+extern "C" int rf_chunk_pass2(rf_ctx* c, int chunk) {
+  if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_pass2: chunked path not configured");
+  if (chunk < 0 || chunk >= c->ck_n) return fail(RF_ERR_ARG, "rf_chunk_pass2: bad chunk");
+  int e = chunk_pass2_impl(c, chunk, 0, c->nxl, chunk);
+  if (e) return e;
   if (chunk == c->ck_n - 1) c->pass2_done = true;   // rf_finish_yz now runs pass 3 only
+  return RF_OK;
+}
+extern "C" int rf_chunk_pass2_x(rf_ctx* c, int chunk, int x0, int x1, int wait_index) {
+  if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_pass2_x: chunked path not configured");
+  if (chunk < 0 || chunk >= c->ck_n || x0 < 0 || x1 > c->nxl || x0 > x1)
+    return fail(RF_ERR_ARG, "rf_chunk_pass2_x: bad chunk or range");
+  return chunk_pass2_impl(c, chunk, x0, x1, wait_index);
+}
+
+// pass 3 of rows x in [x0, x1) once pass 2 of every chunk has been queued for them; `last`
+// closes the step (statistics over all ranges, the field becomes the real-space field)
+extern "C" int rf_chunk_pass3_x(rf_ctx* c, int x0, int x1, const double* zscale, int want_stats, int last) {
+  if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_pass3_x: chunked path not configured");
+  if (x0 < 0 || x1 > c->nxl || x0 > x1) return fail(RF_ERR_ARG, "rf_chunk_pass3_x: bad range");
+  if (!c->pipe || c->nz > 4096) return fail(RF_ERR_STATE, "rf_chunk_pass3_x: pipelined pass 3 not available");
+  const float* zs = nullptr;
+  if (zscale) {
+    if (!c->zs_loaded) {
+      int e = upload_table<float>(c, c->zs_dev, zscale, c->nz);
+      if (e) return e;
+      c->zs_loaded = true;
+    }
+    zs = (const float*)c->zs_dev;
+  }
+  if (want_stats && c->parts_cap < (long long)c->num_sms * 64) {
+    if (c->part_used) return fail(RF_ERR_STATE, "rf_chunk_pass3_x: partials buffer too small");
+    int e = ensure_partials(c, (long long)c->num_sms * 64);
+    if (e) return e;
+  }
+  if (x1 > x0) {
+    pipe::K3PParams q;
+    q.buf = (float*)c->field;
+    q.twH = (const cpx<float>*)c->tw_zh;
+    q.twN = (const cpx<float>*)c->tw_z;
+    q.zscale = zs;
+    q.partials = nullptr;
+    int e = 0;
+    RF_DISPATCH_PIPE(c->nz, {
+      const int lpt = PipeLaunch<NN>::k3p_lines_per_tile();
+      const long long l0 = (long long)x0 * c->ny, l1 = (long long)x1 * c->ny;
+      if (l0 % lpt || l1 % lpt) return fail(RF_ERR_ARG, "rf_chunk_pass3_x: range does not hold whole tiles");
+      q.tile0 = (int)(l0 / lpt);
+      q.ntiles = (int)((l1 - l0) / lpt);
+      const int grid = std::min(q.ntiles, c->num_sms);
+      if (want_stats) {
+        if (c->part_used + grid > c->parts_cap) return fail(RF_ERR_STATE, "rf_chunk_pass3_x: too many ranges");
+        q.partials = c->partials + 2 * c->part_used;
+        c->part_used += grid;
+      }
+      const int sg = seg_begin(c, 2);
+      e = c->k3q ? PipeLaunch<NN>::k3q(q, grid, c->stream) : PipeLaunch<NN>::k3p(q, grid, c->stream);
+      seg_end(c, sg);
+    });
+    c->launches++;
+    RF_CUDA(e);
+  }
+  if (last) {
+    if (want_stats) {
+      c->nparts = c->part_used;
+      stats_final_kernel<<<1, 256, 0, c->stream>>>(c->partials, c->nparts, c->stats_dev);
+      c->launches++;
+      RF_CUDA(cudaGetLastError());
+      c->stats_valid = true;
+    }
+    c->pass2_done = false;
+    c->field_is_real = true;
+  }
   return RF_OK;
 }
 

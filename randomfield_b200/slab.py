@@ -42,6 +42,32 @@ def recv_to_rows(recv, nx, ny, nz, world):
     return np.ascontiguousarray(np.transpose(r, (1, 0, 2, 3)).reshape(nxl, ny, nzc))
 
 
+def split_plan(nxl, world, frac=None, nsub=None, align=1):
+    """x ranges of the split schedule (include/rf_b200.h, rf_chunk_exchange_x): rows [0, xa) of
+    the local x-slab cross NVLink while pass 1 runs, the rest afterwards in `nsub` ranges whose
+    pass 2 + pass 3 overlap the next range's transfer.  Returns (xa, [(x0, x1), ...]);
+    no ranges = the plain chunked schedule.  Range edges are multiples of `align` rows (pass 3
+    works on whole 64 KB tiles of lines).  Defaults: split only where the exchange, not the
+    kernels, bounds the step (4 ranks and more: 3/4 and more of the field leaves each GPU)."""
+    if frac is None:
+        frac = float(os.environ.get("RF_SPLIT_A", "0.45" if world >= 4 else "1"))
+    if nsub is None:
+        nsub = int(os.environ.get("RF_SPLIT_NSUB", "4"))
+    units = nxl // align if align > 0 and nxl % align == 0 else 0
+    if not 0.0 < frac < 1.0 or nsub < 1 or units < 2:
+        return nxl, []
+    ua = min(units - 1, max(1, int(round(frac * units))))
+    nsub = min(nsub, units - ua)
+    edges = [align * (ua + ((units - ua) * i) // nsub) for i in range(nsub + 1)]
+    return align * ua, [(edges[i], edges[i + 1]) for i in range(nsub) if edges[i + 1] > edges[i]]
+
+
+def pass3_row_align(ny, nz):
+    """x rows per whole number of pass-3 tiles (64 KB of packed half-complex lines)."""
+    lines_per_tile = max(1, 65536 // (nz // 2 * 8))
+    return lines_per_tile // np.gcd(lines_per_tile, ny)
+
+
 def all_to_all(send, recv, group=None):
     """One all-to-all of `world` equal contiguous blocks (torch tensors, any backend)."""
     import torch.distributed as dist
@@ -96,6 +122,8 @@ class SlabEngine(object):
                     want //= 2
             if not self.nchunks:
                 mode = "nccl"
+        self._xa, self._subs = (split_plan(nx // self.world, self.world, align=pass3_row_align(ny, nz))
+                                if mode == "chunked" else (nx // self.world, []))
         self.mode = mode
         self.direct = mode == "direct"
         self._peer_ptrs = []
@@ -129,20 +157,32 @@ class SlabEngine(object):
             else:
                 if self.mode == "chunked":
                     eng, q = self.engine, self._comm
-                    eng.chunk_begin_step()
-                    with torch.cuda.stream(q):
-                        # peers have finished reading their receive buffers (previous step)
-                        dist.all_reduce(self._fence, group=self.group)
-                    for c in range(self.nchunks):
-                        eng.chunk_xpass(seed, potential, c)
-                        eng.chunk_exchange(c)
+                    nc, xa, subs = self.nchunks, self._xa, self._subs
+
+                    def fence():
                         with torch.cuda.stream(q):
-                            # every rank's copies of chunk c have landed
                             dist.all_reduce(self._fence, group=self.group)
+
+                    eng.chunk_begin_step()
+                    fence()      # peers have finished reading their receive buffers (previous step)
+                    for c in range(nc):
+                        eng.chunk_xpass(seed, potential, c)
+                        eng.chunk_exchange_x(c, 0, xa, True)
+                        fence()  # every rank's copies of chunk c have landed
                         eng.chunk_arrived(c)
                         if c >= 1:
-                            eng.chunk_pass2(c - 1)
-                    eng.chunk_pass2(self.nchunks - 1)
+                            eng.chunk_pass2_x(c - 1, 0, xa, c - 1)
+                    eng.chunk_pass2_x(nc - 1, 0, xa, nc - 1)
+                    for s, (x0, x1) in enumerate(subs):
+                        eng.chunk_exchange_x(-1, x0, x1, False)
+                        fence()
+                        eng.chunk_arrived(nc + s)
+                    eng.chunk_pass3_x(0, xa, zscale, want_stats, last=not subs)
+                    for s, (x0, x1) in enumerate(subs):
+                        for c in range(nc):
+                            eng.chunk_pass2_x(c, x0, x1, nc + s if c == 0 else -1)
+                        eng.chunk_pass3_x(x0, x1, zscale, want_stats, last=s == len(subs) - 1)
+                    return
                 elif self.direct:
                     # peers have finished reading their receive buffers (previous step) ...
                     dist.all_reduce(self._fence, group=self.group)
@@ -171,7 +211,7 @@ class SlabEngine(object):
 
 
 def run_virtual_slabs(nx, ny, nz, spacing, power, seed, world, smoothing=0.0, dtype=np.float32,
-                      potential=False, zscale=None, direct=False, chunks=0):
+                      potential=False, zscale=None, direct=False, chunks=0, split=None):
     """All `world` ranks of the slab pipeline driven from ONE process on ONE GPU: each rank's
     engine generates its y-slab, the all-to-all is done with device copies between the
     engines' buffers, each rank finishes its x-slab.  Returns (field (nx, ny, nz), mean, std).
@@ -194,16 +234,26 @@ def run_virtual_slabs(nx, ny, nz, spacing, power, seed, world, smoothing=0.0, dt
             for r, peer in enumerate(engines):
                 e.set_peer_recv(r, peer.device_ptr(_lib.RF_BUF_RECV))
             e.chunk_config(chunks)
+        xa, subs = (split_plan(nx // world, world, *split, align=pass3_row_align(ny, nz)) if split
+                    else (nx // world, []))
         for e in engines:
             e.chunk_begin_step()
             for c in range(chunks):
                 e.chunk_xpass(seed, potential, c)
-                e.chunk_exchange(c)
+                e.chunk_exchange_x(c, 0, xa, True)
+            for x0, x1 in subs:
+                e.chunk_exchange_x(-1, x0, x1, False)
         torch.cuda.synchronize()
         for e in engines:
             for c in range(chunks):
                 e.chunk_arrived(c)
-                e.chunk_pass2(c)
+                e.chunk_pass2_x(c, 0, xa, c)
+            e.chunk_pass3_x(0, xa, zscale, True, last=not subs)
+            for s, (x0, x1) in enumerate(subs):
+                e.chunk_arrived(chunks + s)
+                for c in range(chunks):
+                    e.chunk_pass2_x(c, x0, x1, chunks + s if c == 0 else -1)
+                e.chunk_pass3_x(x0, x1, zscale, True, last=s == len(subs) - 1)
     for e in engines:
         if chunks:
             break
@@ -221,9 +271,7 @@ def run_virtual_slabs(nx, ny, nz, spacing, power, seed, world, smoothing=0.0, dt
     n = 0
     parts = []
     for e in engines:
-        if world > 1:
-            e.finish_yz(zscale, True)
-        else:
+        if not chunks:
             e.finish_yz(zscale, True)
         a, b, c = e.stats()
         s1, s2, n = s1 + a, s2 + b, n + c

@@ -53,6 +53,36 @@ def test_chunked_exchange_bit_identical(shape, chunks):
         assert abs(std - std1) <= 1e-9 * std1
 
 
+@pytest.mark.parametrize("shape,chunks,split", [((256, 256, 128), 4, (0.4, 3)), ((128, 256, 128), 2, (0.5, 64)),
+                                                ((2048, 128, 128), 2, (0.3, 2)), ((128, 2048, 128), 2, (0.7, 1))])
+def test_split_schedule_bit_identical(shape, chunks, split):
+    """The exchange also cut along the destination's x axis (rf_chunk_exchange_x / pass2_x /
+    pass3_x: rows [0, xa) travel with pass 1, the rest afterwards in x ranges): same bits, and
+    the statistics summed over the ranges' pass-3 launches agree."""
+    from randomfield_b200 import slab
+    power = oracle.load_default_power()
+    zs = np.linspace(0.5, 1.5, shape[2])
+    ref, _, std1 = slab.run_virtual_slabs(*shape, 2.0, power, seed=99, world=1, zscale=zs)
+    for world in (1, 2, 4, 8):
+        got, _, std = slab.run_virtual_slabs(*shape, 2.0, power, seed=99, world=world, chunks=chunks,
+                                             split=split, zscale=zs)
+        assert np.array_equal(got, ref), "world=%d" % world
+        assert abs(std - std1) <= 1e-9 * std1
+
+
+def test_split_plan_covers_the_slab():
+    from randomfield_b200 import slab
+    for nxl in (1, 2, 16, 512):
+        for frac in (0.1, 0.45, 0.9, 1.0):
+            for nsub in (1, 4, 1000):
+                for align in (1, 2, 4):
+                    xa, subs = slab.split_plan(nxl, 8, frac, nsub, align)
+                    edges = [0, xa] + [b for _, b in subs]
+                    assert edges[-1] == nxl and all(b > a for a, b in zip(edges, edges[1:]))
+                    assert all(a == pb for (a, _), pb in zip(subs, edges[1:]))
+                    assert all(e % align == 0 for e in edges) or not subs
+
+
 def test_slab_field_matches_oracle():
     """and the decomposed field is the right field: Philox restatement + numpy irfftn."""
     from randomfield_b200 import slab
@@ -97,20 +127,24 @@ def _ngpu():
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs two GPUs")
-@pytest.mark.parametrize("direct", ["1", "0", "chunked"])
+@pytest.mark.parametrize("direct", ["1", "0", "chunked", "split"])
 def test_nccl_two_ranks_matches_single(tmp_path, direct):
     """Real one-process-per-GPU run (direct peer stores, the NCCL all-to-all, and the chunked
     copy-engine exchange): rank slabs written to disk, compared with world=1."""
     script = os.path.join(ROOT, "tests", "multi_worker.py")
     out = str(tmp_path)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
-           "--master-addr", "127.0.0.1", "--master-port", {"1": "29533", "0": "29535"}.get(direct, "29537"), script, out]
-    env = dict(os.environ, RF_EXCHANGE="chunked", RF_CHUNKS="2") if direct == "chunked" else dict(
-        os.environ, RF_DIRECT=direct)
+           "--master-addr", "127.0.0.1", "--master-port",
+           {"1": "29533", "0": "29535", "split": "29539"}.get(direct, "29537"), script, out]
+    env = dict(os.environ, RF_DIRECT=direct)
+    if direct in ("chunked", "split"):
+        env = dict(os.environ, RF_EXCHANGE="chunked", RF_CHUNKS="2")
+    if direct == "split":   # rows [0, 64) with pass 1, then two ranges of 32 rows
+        env.update(RF_SPLIT_A="0.5", RF_SPLIT_NSUB="2")
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode == 0, r.stdout + r.stderr
     from randomfield_b200 import slab
-    assert open(os.path.join(out, "mode.txt")).read() == {"1": "direct", "0": "nccl"}.get(direct, direct)
+    assert open(os.path.join(out, "mode.txt")).read() == {"1": "direct", "0": "nccl", "split": "chunked"}.get(direct, direct)
     ref, _, std1 = slab.run_virtual_slabs(256, 256, 128, 2.0, oracle.load_default_power(), seed=42, world=1)
     got = np.concatenate([np.load(os.path.join(out, "rank%d.npy" % r)) for r in range(2)], axis=0)
     assert np.array_equal(got, ref)
