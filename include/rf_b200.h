@@ -184,11 +184,12 @@ int rf_chunk_pass2(rf_ctx* ctx, int chunk);
  *   rf_chunk_pass2_x(last, 0, xa, last)
  *   for every range s: rf_chunk_exchange_x(-1, x0, x1, 0); [fence]; rf_chunk_arrived(nchunks + s)
  *   rf_chunk_pass3_x(0, xa, ..., last = 0)
- *   for every range s: for c: rf_chunk_pass2_x(c, x0, x1, c == 0 ? nchunks + s : -1);
+ *   for every range s: rf_chunk_pass2_x(-1, x0, x1, nchunks + s);     (every chunk, one launch)
  *                      rf_chunk_pass3_x(x0, x1, ..., last = (s is the final range))
  * Same kernels on the same data as the plain chunked plan: the field is bit-identical. */
 int rf_chunk_exchange_x(rf_ctx* ctx, int chunk /* -1: every chunk */, int x0, int x1, int wait_pass1);
-int rf_chunk_pass2_x(rf_ctx* ctx, int chunk, int x0, int x1, int wait_index /* of rf_chunk_arrived, -1: none */);
+int rf_chunk_pass2_x(rf_ctx* ctx, int chunk /* -1: every chunk */, int x0, int x1,
+                     int wait_index /* of rf_chunk_arrived, -1: none */);
 int rf_chunk_pass3_x(rf_ctx* ctx, int x0, int x1, const double* zscale, int want_stats, int last);
 
 /* raw device pointers for zero-copy wrapping (torch / DLPack) and for the all-to-all */

@@ -1231,7 +1231,8 @@ extern "C" int rf_chunk_arrived(rf_ctx* c, int chunk) {
   return RF_OK;
 }
 
-// pass 2 of rows x in [x0, x1) of one chunk; waits for event `ev` of rf_chunk_arrived first (ev >= 0)
+// pass 2 of rows x in [x0, x1) of one chunk (chunk < 0: of every chunk, in one launch); waits for
+// event `ev` of rf_chunk_arrived first (ev >= 0)
 static int chunk_pass2_impl(rf_ctx* c, int chunk, int x0, int x1, int ev) {
   if (ev >= 0) {
     if (ev >= (int)c->ev_xc.size() || !c->ev_xc[ev])
@@ -1240,14 +1241,16 @@ static int chunk_pass2_impl(rf_ctx* c, int chunk, int x0, int x1, int ev) {
   }
   if (x1 <= x0) return RF_OK;
   const int nzc = c->nz / 2, wc = nzc / c->ck_n;
+  const int nck = chunk < 0 ? c->ck_n : 1;
   pipe::K2PParams q;
   q.tw = (const cpx<float>*)c->tw_y;
   q.out = (cpx<float>*)c->field;
   q.out_outer = (long long)c->ny * nzc;
   q.out_row = nzc;
-  q.z_out_base = chunk * wc;
+  q.z_out_base = chunk < 0 ? 0 : chunk * wc;
   const size_t chunk_elems = (size_t)c->nx * c->nyl * wc;
-  const cpx<float>* in = (const cpx<float>*)(c->world > 1 ? c->recv : c->send) + (size_t)chunk * chunk_elems;
+  const cpx<float>* in = (const cpx<float>*)(c->world > 1 ? c->recv : c->send) +
+                         (size_t)(chunk < 0 ? 0 : chunk) * chunk_elems;
   q.rows_per_src = c->world > 1 ? c->nyl : c->ny;
   int e = 0;
   CUtensorMap min, mout;
@@ -1255,11 +1258,15 @@ static int chunk_pass2_impl(rf_ctx* c, int chunk, int x0, int x1, int ev) {
     const int tz = PipeLaunch<NN>::tile_cols();
     q.ztiles = wc / tz;
     q.tile0 = x0 * q.ztiles;
-    q.ntiles = (x1 - x0) * q.ztiles;
+    q.ck_tiles = (x1 - x0) * q.ztiles;
+    q.ck_wc = wc;
+    q.ntiles = nck * q.ck_tiles;
     q.box_rows = std::min(PipeLaunch<NN>::box_rows(), q.rows_per_src);
     const int nsrc = c->ny / q.rows_per_src;
-    // [src][nxl][rows_per_src][wc]; single GPU: [nx][ny][wc]
-    uint64_t din[4] = {(uint64_t)2 * wc, (uint64_t)q.rows_per_src, (uint64_t)c->nxl, (uint64_t)nsrc};
+    q.nsrc = nsrc;
+    // [chunk][src][nxl][rows_per_src][wc] (single GPU: [chunk][nx][ny][wc]); a chunk's source
+    // blocks follow the previous chunk's, so (chunk, src) is one dimension of the map
+    uint64_t din[4] = {(uint64_t)2 * wc, (uint64_t)q.rows_per_src, (uint64_t)c->nxl, (uint64_t)nsrc * nck};
     uint64_t sin[3] = {(uint64_t)wc * 8, (uint64_t)q.rows_per_src * wc * 8,
                        (uint64_t)c->nxl * q.rows_per_src * wc * 8};
     uint32_t bin[4] = {(uint32_t)2 * tz, (uint32_t)q.box_rows, 1, 1};
@@ -1289,7 +1296,7 @@ extern "C" int rf_chunk_pass2(rf_ctx* c, int chunk) {
 }
 extern "C" int rf_chunk_pass2_x(rf_ctx* c, int chunk, int x0, int x1, int wait_index) {
   if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_pass2_x: chunked path not configured");
-  if (chunk < 0 || chunk >= c->ck_n || x0 < 0 || x1 > c->nxl || x0 > x1)
+  if (chunk >= c->ck_n || x0 < 0 || x1 > c->nxl || x0 > x1)
     return fail(RF_ERR_ARG, "rf_chunk_pass2_x: bad chunk or range");
   return chunk_pass2_impl(c, chunk, x0, x1, wait_index);
 }

@@ -234,12 +234,12 @@ k2b_strided_fft(const __grid_constant__ CUtensorMap map_in, const K2PParams p) {
   const int first = blockIdx.x, step = gridDim.x;
   // rows [lo, hi) of tile t -> dst (dense position of row r: dst + r*TZ), completion on bar
   auto load_rows = [&](int t, int lo, int hi, cpx<float>* dst, uint64_t* bar) {
-    t += p.tile0;
-    const int o = t / p.ztiles, z0 = (t % p.ztiles) * TZ;
+    int ck, o, z0;
+    p.decode(t, ck, o, z0, TZ);
     pipe::mbar_expect_tx(bar, (uint32_t)((hi - lo) * TZ * 8));
     for (int r0 = lo; r0 < hi; r0 += p.box_rows) {
       const int src = r0 / p.rows_per_src, rl = r0 - src * p.rows_per_src;
-      pipe::tma_load_4d(dst + r0 * TZ, &map_in, bar, 2 * z0, rl, o, src);
+      pipe::tma_load_4d(dst + r0 * TZ, &map_in, bar, 2 * z0, rl, o, ck * p.nsrc + src);
     }
   };
   if (tid == 0 && first < p.ntiles) {
@@ -276,8 +276,9 @@ k2b_strided_fft(const __grid_constant__ CUtensorMap map_in, const K2PParams p) {
     step_c_read<N>(buf, tid, u);
     __syncthreads();
     if (tid == 0 && t + step < p.ntiles) load_rows(t + step, kSplit, N, buf, &full[1]);
-    const int tt = t + p.tile0;
-    cpx<float>* const outp = p.out + (size_t)(tt / p.ztiles) * p.out_outer + (tt % p.ztiles) * TZ + p.z_out_base;
+    int ck, oo, zz;
+    p.decode(t, ck, oo, zz, TZ);
+    cpx<float>* const outp = p.out + (size_t)oo * p.out_outer + zz + p.z_out_base + ck * p.ck_wc;
     sfor<0, G::IC>([&](auto qi) {
       constexpr int q = decltype(qi)::value;
       const int w = tid + q * kThreads;

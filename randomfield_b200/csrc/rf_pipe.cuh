@@ -494,6 +494,17 @@ struct K2PParams {
   int rows_per_src;        // rows of a line held by one source block (N when single GPU)
   int box_rows;            // rows per TMA box = min(256, rows_per_src)
   int z_out_base;          // column offset of this launch in the output (chunked runs)
+  // one launch over several chunks of the chunk-major receive buffer (split schedule): tile t
+  // belongs to chunk t / ck_tiles, whose source blocks follow the previous chunk's in the load
+  // map's last dimension and whose columns start ck_wc further right in the output
+  int ck_tiles = 0x7fffffff, ck_wc = 0, nsrc = 1;
+  // tile t of the launch -> chunk, outer index, first column (within the chunk)
+  __device__ __forceinline__ void decode(int t, int& ck, int& o, int& z0, int tz) const {
+    ck = t / ck_tiles;
+    const int r = t - ck * ck_tiles + tile0;
+    o = r / ztiles;
+    z0 = (r - o * ztiles) * tz;
+  }
   // output addressing for kernels that store from registers (rf_big.cuh): element
   // out[outer * out_outer + row * out_row + column]
   cpx<float>* out;
@@ -535,12 +546,13 @@ k2p_strided_fft(const __grid_constant__ CUtensorMap map_in, const __grid_constan
       tma_prefetch_desc(&map_in);
       tma_prefetch_desc(&map_out);
       auto load_tile = [&](int t, int b) {
-        t += p.tile0;
-        const int o = t / p.ztiles, z0 = (t % p.ztiles) * P::TZ;
+        int ck, o, z0;
+        p.decode(t, ck, o, z0, P::TZ);
         mbar_expect_tx(&full[b], (uint32_t)P::kDenseBytes);
         for (int r0 = 0; r0 < N; r0 += p.box_rows) {
           const int src = r0 / p.rows_per_src, rl = r0 - src * p.rows_per_src;
-          tma_load_4d(dense0 + b * kDenseElems + r0 * P::TZ, &map_in, &full[b], 2 * z0, rl, o, src);
+          tma_load_4d(dense0 + b * kDenseElems + r0 * P::TZ, &map_in, &full[b], 2 * z0, rl, o,
+                      ck * p.nsrc + src);
         }
       };
       int n = 0;
@@ -549,9 +561,11 @@ k2p_strided_fft(const __grid_constant__ CUtensorMap map_in, const __grid_constan
       for (int t = first; t < p.ntiles; t += step, ++i) {
         const int b = i & 1;
         mbar_wait(&done[b], (i >> 1) & 1);
-        const int o = (t + p.tile0) / p.ztiles, z0 = ((t + p.tile0) % p.ztiles) * P::TZ;
+        int ck, o, z0;
+        p.decode(t, ck, o, z0, P::TZ);
         for (int r0 = 0; r0 < N; r0 += P::kBoxRows)
-          tma_store_3d(&map_out, dense0 + b * kDenseElems + r0 * P::TZ, 2 * (z0 + p.z_out_base), r0, o);
+          tma_store_3d(&map_out, dense0 + b * kDenseElems + r0 * P::TZ,
+                       2 * (z0 + p.z_out_base + ck * p.ck_wc), r0, o);
         bulk_commit();
         const int t2 = t + 2 * step;
         if (t2 < p.ntiles) {

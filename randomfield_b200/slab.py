@@ -179,8 +179,7 @@ class SlabEngine(object):
                         eng.chunk_arrived(nc + s)
                     eng.chunk_pass3_x(0, xa, zscale, want_stats, last=not subs)
                     for s, (x0, x1) in enumerate(subs):
-                        for c in range(nc):
-                            eng.chunk_pass2_x(c, x0, x1, nc + s if c == 0 else -1)
+                        eng.chunk_pass2_x(-1, x0, x1, nc + s)
                         eng.chunk_pass3_x(x0, x1, zscale, want_stats, last=s == len(subs) - 1)
                     return
                 elif self.direct:
@@ -251,8 +250,7 @@ def run_virtual_slabs(nx, ny, nz, spacing, power, seed, world, smoothing=0.0, dt
             e.chunk_pass3_x(0, xa, zscale, True, last=not subs)
             for s, (x0, x1) in enumerate(subs):
                 e.chunk_arrived(chunks + s)
-                for c in range(chunks):
-                    e.chunk_pass2_x(c, x0, x1, chunks + s if c == 0 else -1)
+                e.chunk_pass2_x(-1, x0, x1, chunks + s)
                 e.chunk_pass3_x(x0, x1, zscale, True, last=s == len(subs) - 1)
     for e in engines:
         if chunks:
