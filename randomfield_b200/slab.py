@@ -47,10 +47,12 @@ def split_plan(nxl, world, frac=None, nsub=None, align=1):
     the local x-slab cross NVLink while pass 1 runs, the rest afterwards in `nsub` ranges whose
     pass 2 + pass 3 overlap the next range's transfer.  Returns (xa, [(x0, x1), ...]);
     no ranges = the plain chunked schedule.  Range edges are multiples of `align` rows (pass 3
-    works on whole 64 KB tiles of lines).  Defaults: split only where the exchange, not the
-    kernels, bounds the step (4 ranks and more: 3/4 and more of the field leaves each GPU)."""
+    works on whole 64 KB tiles of lines).  Opt-in (RF_SPLIT_A = fraction of rows sent with pass 1,
+    RF_SPLIT_NSUB = later ranges): measured on B200 x4 / x8 the step is bound by the kernels and
+    by the copy engines' share of HBM at about the same level, so hiding pass 3 behind the tail
+    of the transfer gains 1 % at 8 ranks and loses 1 % at 4."""
     if frac is None:
-        frac = float(os.environ.get("RF_SPLIT_A", "0.45" if world >= 4 else "1"))
+        frac = float(os.environ.get("RF_SPLIT_A", "1"))
     if nsub is None:
         nsub = int(os.environ.get("RF_SPLIT_NSUB", "4"))
     units = nxl // align if align > 0 and nxl % align == 0 else 0
