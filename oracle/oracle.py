@@ -5,7 +5,7 @@ cpu_baseline / --impl reference legs may use it, and only as the checker or the 
 Part 1 restates, in plain numpy, the reference algorithm (dkirkby/randomfield @ aa97035):
 every function cites the reference file:line it follows.  Parity status: PINNED -- the
 restatement is checked bit-for-bit against the unmodified reference modules run in the build
-container (oracle/ref_replay.py, tests/test_oracle_vs_reference.py) and against the golden
+container (oracle/ref_replay.py, tests/test_oracle.py::test_oracle_matches_reference_bitwise) and against the golden
 fixtures committed under tests/golden/ (generated from the reference by
 tests/golden/make_golden.py).  The reference's own tests hold no stored vectors; its
 known-answer test (tests/test_generate.py:24-62, Gaussian-P(k) variance) is re-hosted in
