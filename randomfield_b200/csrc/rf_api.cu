@@ -41,7 +41,8 @@ struct rf_ctx {
   int nxl = 0, nyl = 0;     // local slab extents
   bool fast = false;
   bool pipe = false;        // TMA-pipelined kernels (f32, env RF_PIPE != 0)
-  bool fuse = false;        // fused y+z kernel k23p (env RF_FUSE != 0)
+  bool fuse = false;        // fused y+z kernel k23p (env RF_FUSE=1) / k23q (RF_FUSE=2)
+  bool fuse_q = false;      // ... the three-deep in-place ring variant
   bool k1q = true;          // pass 1 with two CTAs per SM (env RF_K1Q=0: one-CTA k1p)
   bool k3q = true;          // pass 3 with the three-deep in-place ring (env RF_K3Q=0: k3p)
   bool fuse12 = false;      // passes 1 + 2 in one kernel when nx == ny in {512, 1024}, single GPU (env RF_FUSE12=1)
@@ -151,7 +152,8 @@ extern "C" int rf_create(int nx, int ny, int nz, int dtype, int rank, int world,
     c->pipe = c->fast && dtype == RF_F32 && !(env && env[0] == '0');
     const char* envf = getenv("RF_FUSE");
     // opt-in: measured slower than k2p + k3p on B200, kept for the L2-reuse work
-    c->fuse = c->pipe && ny <= 1024 && nz <= 2048 && envf && envf[0] == '1';
+    c->fuse = c->pipe && ny <= 1024 && nz <= 2048 && envf && (envf[0] == '1' || envf[0] == '2');
+    c->fuse_q = c->fuse && envf[0] == '2';
     const char* envq = getenv("RF_K1Q");
     c->k1q = !(envq && envq[0] == '0');
     // opt-in: measured slower than k1q + k2p on B200
@@ -939,6 +941,9 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
             f.t3 = t3_per_plane;
             // far enough apart that a plane's y pass has normally drained when its z pass starts
             f.lag = std::min(c->nxl, std::max(1, (3 * c->num_sms) / (f.t2 + f.t3) + 1));
+            // k23q: three tiles in flight per CTA and signals up to four stores late -> measured
+            // plateau from about ten rounds of tickets between a plane's y and z pass (52 MB of L2)
+            if (c->fuse_q) f.lag = std::min(c->nxl, std::max(1, (11 * c->num_sms) / (f.t2 + f.t3) + 1));
             if (const char* el = getenv("RF_LAG")) f.lag = std::min(c->nxl, std::max(1, atoi(el)));
             if (!c->sched) RF_CUDA(cudaMalloc((void**)&c->sched, sizeof(unsigned int) * (1 + c->nxl)));
             RF_CUDA(cudaMemsetAsync(c->sched, 0, sizeof(unsigned int) * (1 + c->nxl), c->stream));
@@ -952,7 +957,9 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
               f.k3.partials = c->partials;
             }
             mark(c, 2);
-            if constexpr (NN <= 1024) e = PipeLaunch<NN>::k23p(c->nz, min, mout, f, grid, c->stream);
+            if constexpr (NN <= 1024)
+              e = c->fuse_q ? PipeLaunch<NN>::k23q(c->nz, min, mout, f, grid, c->stream)
+                            : PipeLaunch<NN>::k23p(c->nz, min, mout, f, grid, c->stream);
             mark(c, 3);
             mark(c, 4);
             mark(c, 5);

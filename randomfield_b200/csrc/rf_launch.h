@@ -7,6 +7,7 @@
 #include "rf_big.cuh"
 #include "rf_fuse12.cuh"
 #include "rf_k3q.cuh"
+#include "rf_k23q.cuh"
 
 namespace rf {
 
@@ -31,6 +32,9 @@ struct PipeLaunch {
   static int k1p(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s);
   // fused y + z pass (this N = ny); nz in 64..2048
   static int k23p(int nz, const CUtensorMap& in, const CUtensorMap& out, const pipe::K23Params& p, int grid,
+                  cudaStream_t s);
+  // same with in-place tile bodies and a three-deep ring (rf_k23q.cuh)
+  static int k23q(int nz, const CUtensorMap& in, const CUtensorMap& out, const pipe::K23Params& p, int grid,
                   cudaStream_t s);
   // two-CTAs-per-SM variant of k1p; hinge_cells = entries of the sigma cell table staged in
   // shared memory.  k1q_fits() says whether that table fits next to the work buffer.

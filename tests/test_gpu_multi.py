@@ -121,6 +121,23 @@ def test_fused_pass12_kernel_matches(monkeypatch):
         assert err <= 1e-6
 
 
+@pytest.mark.parametrize("mode", ["1", "2"])
+@pytest.mark.parametrize("shape", [(64, 256, 256), (128, 1024, 128), (64, 64, 2048), (256, 512, 1024)])
+def test_fused_yz_kernels_bit_identical(monkeypatch, mode, shape):
+    """Opt-in fused pass-2 + pass-3 kernels (RF_FUSE=1: k23p, two-buffer ring; RF_FUSE=2: k23q,
+    in-place tiles in a three-deep ring): same arithmetic in the same order as k2p + k3q."""
+    from randomfield_b200 import slab
+    power = oracle.load_default_power()
+    zs = np.linspace(0.5, 1.5, shape[2])
+    monkeypatch.setenv("RF_FUSE", "0")
+    ref, _, std1 = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1, zscale=zs)
+    monkeypatch.setenv("RF_FUSE", mode)
+    for world in (1, 2):
+        got, _, std = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=world, zscale=zs)
+        assert np.array_equal(got, ref), "world=%d" % world
+        assert abs(std - std1) <= 1e-9 * std1
+
+
 def _ngpu():
     import torch
     return torch.cuda.device_count()
