@@ -200,6 +200,9 @@ int rf_is_fast(rf_ctx* ctx);
 /* 1 if the hot path runs on the persistent TMA-pipelined kernels (k1p/k2p/k3p: float32, axes of
  * 64..1024 points, 2048 for z), 0 if on the rf_fast.cuh tile kernels or the generic path */
 int rf_is_pipelined(rf_ctx* ctx);
+/* 0: passes 2 and 3 are separate kernels; 2 / 1: fused in k23q_fused_yz / k23p_fused_yz (whole-field
+ * rf_finish_yz only; the chunked exchange always runs them separately) */
+int rf_is_fused(rf_ctx* ctx);
 /* number of kernels launched by this context so far */
 long long rf_launch_count(rf_ctx* ctx);
 

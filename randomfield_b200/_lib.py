@@ -68,6 +68,7 @@ SIGNATURES = {
     "rf_chunk_pass3_x": (_c.c_int, [_P, _c.c_int, _c.c_int, _P, _c.c_int, _c.c_int]),
     "rf_is_fast": (_c.c_int, [_P]),
     "rf_is_pipelined": (_c.c_int, [_P]),
+    "rf_is_fused": (_c.c_int, [_P]),
     "rf_launch_count": (_c.c_longlong, [_P]),
 }
 
@@ -314,6 +315,11 @@ class Engine:
     @property
     def is_pipelined(self):
         return bool(lib().rf_is_pipelined(self._ctx))
+
+    @property
+    def fused_yz(self):
+        """0: separate pass-2 / pass-3 kernels, 2: k23q_fused_yz, 1: k23p_fused_yz."""
+        return int(lib().rf_is_fused(self._ctx))
 
     @property
     def launch_count(self):

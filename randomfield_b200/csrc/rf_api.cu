@@ -151,9 +151,19 @@ extern "C" int rf_create(int nx, int ny, int nz, int dtype, int rank, int world,
     const char* env = getenv("RF_PIPE");
     c->pipe = c->fast && dtype == RF_F32 && !(env && env[0] == '0');
     const char* envf = getenv("RF_FUSE");
-    // opt-in: measured slower than k2p + k3p on B200, kept for the L2-reuse work
-    c->fuse = c->pipe && ny <= 1024 && nz <= 2048 && envf && (envf[0] == '1' || envf[0] == '2');
-    c->fuse_q = c->fuse && envf[0] == '2';
+    // Passes 2 and 3 in one kernel, the z pass reading the y-pass output from L2.
+    //   RF_FUSE=2: k23q (in-place tiles, three-deep ring, loader + storer warps, dynamic tickets);
+    //              default where it was measured faster than k2p + k3q: both axes <= 1024 and a
+    //              field of 2^26 cells or more (1024^3: 2.77 ms against 2.97 ms);
+    //   RF_FUSE=1: k23p (two-buffer ring; slower, kept for comparison);  RF_FUSE=0: separate kernels.
+    const bool fuse_ok = c->pipe && ny <= 1024 && nz <= 2048 && nz >= 128;
+    const long long cells_local = (long long)(nx / world) * ny * nz;
+    if (envf) {
+      c->fuse = fuse_ok && (envf[0] == '1' || envf[0] == '2');
+      c->fuse_q = c->fuse && envf[0] == '2';
+    } else {
+      c->fuse = c->fuse_q = fuse_ok && nz <= 1024 && cells_local >= (1LL << 26);
+    }
     const char* envq = getenv("RF_K1Q");
     c->k1q = !(envq && envq[0] == '0');
     // opt-in: measured slower than k1q + k2p on B200
@@ -304,6 +314,7 @@ extern "C" int rf_is_fast(rf_ctx* c) { return c && c->fast ? 1 : 0; }
 extern "C" int rf_is_pipelined(rf_ctx* c) {
   return c && c->pipe && c->nx <= 4096 && c->ny <= 4096 && c->nz <= 4096 ? 1 : 0;
 }
+extern "C" int rf_is_fused(rf_ctx* c) { return c && c->fuse ? (c->fuse_q ? 2 : 1) : 0; }
 extern "C" long long rf_launch_count(rf_ctx* c) { return c ? c->launches : 0; }
 extern "C" long long rf_field_elems(rf_ctx* c) {
   return c ? (long long)c->nxl * c->ny * c->nz : 0;
@@ -941,9 +952,9 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
             f.t3 = t3_per_plane;
             // far enough apart that a plane's y pass has normally drained when its z pass starts
             f.lag = std::min(c->nxl, std::max(1, (3 * c->num_sms) / (f.t2 + f.t3) + 1));
-            // k23q: three tiles in flight per CTA and signals up to four stores late -> measured
-            // plateau from about ten rounds of tickets between a plane's y and z pass (52 MB of L2)
-            if (c->fuse_q) f.lag = std::min(c->nxl, std::max(1, (11 * c->num_sms) / (f.t2 + f.t3) + 1));
+            // k23q: measured best with about seven rounds of tickets between a plane's y pass and
+            // its z pass (lag 8 at 1024^3: 32 MB of y-pass output waiting in L2)
+            if (c->fuse_q) f.lag = std::min(c->nxl, std::max(1, (7 * c->num_sms) / (f.t2 + f.t3)));
             if (const char* el = getenv("RF_LAG")) f.lag = std::min(c->nxl, std::max(1, atoi(el)));
             if (!c->sched) RF_CUDA(cudaMalloc((void**)&c->sched, sizeof(unsigned int) * (1 + c->nxl)));
             RF_CUDA(cudaMemsetAsync(c->sched, 0, sizeof(unsigned int) * (1 + c->nxl), c->stream));

@@ -139,15 +139,21 @@ k23q_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant_
 
   if (tid >= kConsumers) {
     if (tid == kConsumers) {
-      // ===== loader: this CTA owns tickets blockIdx.x + n*gridDim.x, in increasing order =====
+      // ===== loader =====
       tma_prefetch_desc(&map_in);
-      unsigned int ticket = blockIdx.x;
+      // Tickets come from a global counter, fetched one tile ahead (the atomic's round trip is
+      // off the critical path).  Unlike a static blockIdx-strided schedule this needs no
+      // co-residency of all CTAs: a ticket is only ever held by a running CTA, a z-pass tile
+      // depends on smaller tickets only, and every CTA works through its tickets in increasing
+      // order -- so the smallest unfinished ticket can always proceed.
+      unsigned int ticket = atomicAdd(p.ticket, 1u);
       int b = 0, ph = 0;
       for (int n = 0;; ++n) {
+        const unsigned int ticket_next = atomicAdd(p.ticket, 1u);
         if (n >= 3) mbar_wait(&empty[b], ph ^ 1);   // (ph flips every 3 tiles: phase of tile n - 3)
         int type, plane, idx;
         k23_decode(p, ticket, type, plane, idx);
-        ticket += gridDim.x;
+        ticket = ticket_next;
         desc[4 * b + 0] = type; desc[4 * b + 1] = plane; desc[4 * b + 2] = idx;
         cpx<float>* dst = buf0 + b * kBufElems;
         if (type == kTileEnd) {
