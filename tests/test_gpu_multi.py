@@ -70,19 +70,6 @@ def test_split_schedule_bit_identical(shape, chunks, split):
         assert abs(std - std1) <= 1e-9 * std1
 
 
-def test_split_plan_covers_the_slab():
-    from randomfield_b200 import slab
-    for nxl in (1, 2, 16, 512):
-        for frac in (0.1, 0.45, 0.9, 1.0):
-            for nsub in (1, 4, 1000):
-                for align in (1, 2, 4):
-                    xa, subs = slab.split_plan(nxl, 8, frac, nsub, align)
-                    edges = [0, xa] + [b for _, b in subs]
-                    assert edges[-1] == nxl and all(b > a for a, b in zip(edges, edges[1:]))
-                    assert all(a == pb for (a, _), pb in zip(subs, edges[1:]))
-                    assert all(e % align == 0 for e in edges) or not subs
-
-
 def test_slab_field_matches_oracle():
     """and the decomposed field is the right field: Philox restatement + numpy irfftn."""
     from randomfield_b200 import slab

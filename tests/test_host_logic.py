@@ -169,3 +169,23 @@ def test_lensing_scan_form_equals_reference_loop(nz, i_min, ok0):
     assert np.all(ref[..., :im] == 0)
     with pytest.raises(ValueError):
         oracle.lensing_potential(dphi, DC, DA, i_min=nz)
+
+
+def test_split_plan_covers_the_slab():
+    from randomfield_b200 import slab
+    for nxl in (1, 2, 16, 512):
+        for frac in (0.1, 0.45, 0.9, 1.0):
+            for nsub in (1, 4, 1000):
+                for align in (1, 2, 4):
+                    xa, subs = slab.split_plan(nxl, 8, frac, nsub, align)
+                    edges = [0, xa] + [b for _, b in subs]
+                    assert edges[-1] == nxl and all(b > a for a, b in zip(edges, edges[1:]))
+                    assert all(a == pb for (a, _), pb in zip(subs, edges[1:]))
+                    assert all(e % align == 0 for e in edges) or not subs
+
+
+def test_pass3_row_align():
+    from randomfield_b200 import slab
+    # 64 KB pass-3 tiles: nz = 64 -> 256 lines per tile, ny = 64 lines per x row -> 4 rows per tile
+    assert slab.pass3_row_align(64, 64) == 4
+    assert slab.pass3_row_align(4096, 4096) == 1 and slab.pass3_row_align(256, 128) == 1
