@@ -125,6 +125,24 @@ def test_fused_yz_kernels_bit_identical(monkeypatch, mode, shape):
         assert abs(std - std1) <= 1e-9 * std1
 
 
+def test_fused_yz_is_the_default_on_large_grids(monkeypatch):
+    """2^26 cells with ny, nz <= 1024: rf_finish_yz runs k23q_fused_yz unless RF_FUSE=0 -- same bits."""
+    from randomfield_b200 import _lib, slab
+    shape = (256, 512, 512)
+    power = oracle.load_default_power()
+    monkeypatch.delenv("RF_FUSE", raising=False)
+    e = _lib.Engine(*shape, dtype=np.float32)
+    assert e.fused_yz == 2
+    e.close()
+    small = _lib.Engine(128, 128, 128, dtype=np.float32)
+    assert small.fused_yz == 0
+    small.close()
+    got, _, std = slab.run_virtual_slabs(*shape, 2.0, power, seed=8, world=1)
+    monkeypatch.setenv("RF_FUSE", "0")
+    ref, _, std0 = slab.run_virtual_slabs(*shape, 2.0, power, seed=8, world=1)
+    assert np.array_equal(got, ref) and abs(std - std0) <= 1e-9 * std0
+
+
 def _ngpu():
     import torch
     return torch.cuda.device_count()
