@@ -952,9 +952,9 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
             f.t3 = t3_per_plane;
             // far enough apart that a plane's y pass has normally drained when its z pass starts
             f.lag = std::min(c->nxl, std::max(1, (3 * c->num_sms) / (f.t2 + f.t3) + 1));
-            // k23q: measured best with about seven rounds of tickets between a plane's y pass and
-            // its z pass (lag 8 at 1024^3: 32 MB of y-pass output waiting in L2)
-            if (c->fuse_q) f.lag = std::min(c->nxl, std::max(1, (7 * c->num_sms) / (f.t2 + f.t3)));
+            // k23q: measured best with about 5.2 rounds of tickets between a plane's y pass and its
+            // z pass (lag 6 at 1024^3, 24 at 512^3: ~25 MB of y-pass output waiting in L2)
+            if (c->fuse_q) f.lag = std::min(c->nxl, std::max(1, (21 * c->num_sms / 4) / (f.t2 + f.t3)));
             if (const char* el = getenv("RF_LAG")) f.lag = std::min(c->nxl, std::max(1, atoi(el)));
             if (!c->sched) RF_CUDA(cudaMalloc((void**)&c->sched, sizeof(unsigned int) * (1 + c->nxl)));
             RF_CUDA(cudaMemsetAsync(c->sched, 0, sizeof(unsigned int) * (1 + c->nxl), c->stream));
