@@ -11,6 +11,10 @@
 #pragma once
 #include "rf_k3q.cuh"
 
+#ifndef RF_K23Q_SIGLAG
+#define RF_K23Q_SIGLAG 4
+#endif
+
 namespace rf {
 namespace pipe {
 
@@ -189,7 +193,7 @@ k23q_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant_
       tma_prefetch_desc(&map_out);
       // planes of the last kSigLag y-pass stores, not yet signalled: a store's completion is only
       // waited for kSigLag tiles later -- or at once when the storer would otherwise sit idle
-      constexpr int kSigLag = 4;
+      constexpr int kSigLag = RF_K23Q_SIGLAG;
       int pend[kSigLag];
 #pragma unroll
       for (int q = 0; q < kSigLag; ++q) pend[q] = -1;
