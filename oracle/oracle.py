@@ -427,6 +427,61 @@ def philox_kfield(shape, spacing, power, seed, smoothing=0.0, potential=False):
     return out, bins
 
 
+def philox_kfield_big(shape, spacing, power, seed, smoothing=0.0, potential=False, slab=16, workers=None):
+    """philox_kfield for grids where its whole-array temporaries do not fit: the same values,
+    built in slabs of `slab` Philox counter rows (each serves ix and ix + nx/2) on a thread pool
+    (numpy ufuncs release the GIL).  Returns the complex128 field only."""
+    import concurrent.futures
+    nx, ny, nz = shape
+    nzh = nz // 2 + 1
+    hx = nx // 2
+    smoothed = filter_power(power, smoothing)
+    _, sig_tab = sigma_table(smoothed, shape, spacing)
+    T = np.float32
+    k0sq = [T((2 * np.pi / (n * spacing)) ** 2) for n in (nx, ny, nz)]
+
+    def jsq(n, idx):
+        j = np.where(idx <= n // 2, idx, idx - n)
+        return (j * j).astype(T)
+
+    jy2 = jsq(ny, np.arange(ny))[None, :, None].astype(np.float64)
+    jz2 = jsq(nz, np.arange(nzh))[None, None, :].astype(np.float64)
+    inner0 = (jz2 * np.float64(k0sq[2])).astype(T)
+    inner1 = (jy2 * np.float64(k0sq[1]) + inner0.astype(np.float64)).astype(T)      # (1, ny, nzh)
+    kseed = int(seed) & 0xFFFFFFFFFFFFFFFF
+    out = np.empty((nx, ny, nzh), dtype=np.complex128)
+    iy = np.arange(ny, dtype=np.uint64)[None, :, None]
+    iz = np.arange(nzh, dtype=np.uint64)[None, None, :]
+
+    def work(p0):
+        p1 = min(hx, p0 + slab)
+        px = np.arange(p0, p1, dtype=np.uint64)[:, None, None]
+        q = (px * np.uint64(ny) + iy) * np.uint64(nzh) + iz
+        w = philox4x32_10(q & _MASK, q >> _S32, 0, 0, kseed & 0xFFFFFFFF, kseed >> 32)
+        for half, (wa, wb) in enumerate(((w[0], w[1]), (w[2], w[3]))):
+            ix = np.arange(p0, p1) + half * hx
+            jx2 = jsq(nx, ix)[:, None, None].astype(np.float64)
+            ksq = (jx2 * np.float64(k0sq[0]) + inner1.astype(np.float64)).astype(T)
+            bins = canonical_bins(ksq, smoothed['k'], T)
+            sig = philox_sigma(ksq, bins, smoothed['k'], sig_tab, shape)
+            if potential:
+                with np.errstate(divide='ignore', invalid='ignore'):
+                    sig = np.where(ksq > 0, sig / ksq.astype(np.float64), 0.0)
+            out[ix[0]:ix[-1] + 1] = sig * box_muller(wa, wb)
+
+    starts = list(range(0, hx, slab))
+    with concurrent.futures.ThreadPoolExecutor(workers or min(16, os.cpu_count() or 4)) as ex:
+        list(ex.map(work, starts))
+    mx, my, slave, vertex = hermitian_pairing(shape)
+    for izp in (0, nz // 2):
+        plane = out[mx, my, izp]
+        plane = np.where(slave, np.conj(plane), plane)
+        plane = np.where(vertex, plane.real + 0j, plane)
+        out[:, :, izp] = plane
+    out[0, 0, 0] = 0.0
+    return out
+
+
 # ------------------------------------------------------------------------------------------
 # part 3: lensing potential (SURVEY.md section 8, row f2).  Parity status: UNPINNED -- the
 # reference's calculate_lensing_potential cannot run here (astropy absent; scipy 1.18 has no

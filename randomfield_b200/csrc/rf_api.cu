@@ -607,13 +607,6 @@ static int ensure_partials(rf_ctx* c, long long n) {
     default: return fail(RF_ERR_ARG, "size not compiled");\
   }
 
-#define RF_DISPATCH_FUSE12(N_, ...)                     \
-  switch (N_) {                                         \
-    case 512: { constexpr int NN = 512; __VA_ARGS__; } break;  \
-    case 1024: { constexpr int NN = 1024; __VA_ARGS__; } break;\
-    default: return fail(RF_ERR_ARG, "size not compiled");\
-  }
-
 #define RF_DISPATCH_N(N_, ...)                          \
   switch (N_) {                                         \
     case 64: { constexpr int NN = 64; __VA_ARGS__; } break;    \
@@ -718,67 +711,6 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
         c->launches++;
         RF_CUDA(e);
         return RF_OK;
-      }
-      if (c->fuse12 && c->world == 1 && !c->direct && c->nx == c->ny && (c->nx == 512 || c->nx == 1024) &&
-          !c->noise && c->hinge_hi >= c->hinge_lo) {
-        bool launched = false;
-        RF_DISPATCH_FUSE12(c->nx, {
-          const int cells = c->hinge_hi - c->hinge_lo + 1;
-          if (PipeLaunch<NN>::k12_fits(cells)) {
-            const int tz = PipeLaunch<NN>::tile_cols();
-            q.ztiles = nzc / tz;
-            q.ntiles = c->ny * q.ztiles;
-            q.nxl = c->nx;
-            fuse12::K12Params f;
-            f.k1 = q;
-            f.tw_y = (const cpx<float>*)c->tw_y;
-            f.nplanes = c->nx;
-            f.hinge_first = c->hinge_lo;
-            f.hinge_cells = cells;
-            f.out = (cpx<float>*)c->field;
-            f.out_outer = (long long)c->ny * nzc;
-            f.out_row = nzc;
-            f.zc = 8;
-            if (const char* ez = getenv("RF_ZC")) f.zc = std::max(1, atoi(ez));
-            while (f.zc > 1 && (q.ztiles % f.zc)) f.zc >>= 1;
-            if (c->sched_n < q.ztiles) {
-              if (c->zt_done) cudaFree(c->zt_done);
-              c->zt_done = nullptr;
-              RF_CUDA(cudaMalloc((void**)&c->zt_done, sizeof(unsigned int) * q.ztiles));
-              c->sched_n = q.ztiles;
-            }
-            f.dbg = 0;
-            if (const char* ed = getenv("RF_K12_DBG")) f.dbg = atoi(ed);
-            RF_CUDA(cudaMemsetAsync(c->zt_done, (f.dbg & 2) ? 0x7f : 0, sizeof(unsigned int) * q.ztiles, c->stream));
-            f.zt_done = c->zt_done;
-            // pass-1 store map (z, y, x), pass-2 load map (z, y rows, x plane, 1), store map (z, y, x plane)
-            uint64_t d1[3] = {(uint64_t)2 * nzc, (uint64_t)c->ny, (uint64_t)c->nx};
-            uint64_t s1[2] = {(uint64_t)nzc * 8, (uint64_t)c->ny * nzc * 8};
-            uint32_t b1[3] = {(uint32_t)2 * tz, 1, (uint32_t)PipeLaunch<NN>::box_rows()};
-            int e2 = make_tensor_map(&mout.m[0], c->field, 3, d1, s1, b1);
-            if (e2) return e2;
-            CUtensorMap min2, mout2;
-            uint64_t d2[4] = {(uint64_t)2 * nzc, (uint64_t)c->ny, (uint64_t)c->nx, 1};
-            uint64_t s2[3] = {(uint64_t)nzc * 8, (uint64_t)c->ny * nzc * 8, (uint64_t)c->nx * c->ny * nzc * 8};
-            uint32_t b2[4] = {(uint32_t)2 * tz, (uint32_t)PipeLaunch<NN>::box_rows(), 1, 1};
-            e2 = make_tensor_map(&min2, c->field, 4, d2, s2, b2);
-            if (e2) return e2;
-            uint32_t b3[3] = {(uint32_t)2 * tz, (uint32_t)PipeLaunch<NN>::box_rows(), 1};
-            e2 = make_tensor_map(&mout2, c->field, 3, d1, s1, b3);
-            if (e2) return e2;
-            const int grid = std::min(q.ntiles, c->num_sms);
-            mark(c, 0);
-            e = PipeLaunch<NN>::k12(potential != 0, mout, min2, mout2, f, grid, c->stream);
-            mark(c, 1);
-            launched = true;
-          }
-        });
-        if (launched) {
-          c->launches++;
-          RF_CUDA(e);
-          c->pass2_done = true;
-          return RF_OK;
-        }
       }
       RF_DISPATCH_PIPE(c->nx, {
         const int tz = PipeLaunch<NN>::tile_cols();
@@ -950,12 +882,10 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
             f.nplanes = c->nxl;
             f.t2 = q.ztiles;
             f.t3 = t3_per_plane;
-            // far enough apart that a plane's y pass has normally drained when its z pass starts
-            f.lag = std::min(c->nxl, std::max(1, (3 * c->num_sms) / (f.t2 + f.t3) + 1));
-            // k23q: measured best with about 5.2 rounds of tickets between a plane's y pass and its
-            // z pass (lag 6 at 1024^3, 24 at 512^3: ~25 MB of y-pass output waiting in L2)
-            if (c->fuse_q) f.lag = std::min(c->nxl, std::max(1, (21 * c->num_sms / 4) / (f.t2 + f.t3)));
-            if (const char* el = getenv("RF_LAG")) f.lag = std::min(c->nxl, std::max(1, atoi(el)));
+            // measured best with about 5.2 rounds of tickets between a plane's y pass and its z pass
+            // (lag 6 at 1024^3, 24 at 512^3: ~25 MB of y-pass output waiting in L2)
+            f.lag = std::min(c->nxl, std::max(1, (21 * c->num_sms / 4) / (f.t2 + f.t3)));
+            if (c->env_lag > 0) f.lag = std::min(c->nxl, c->env_lag);
             if (!c->sched) RF_CUDA(cudaMalloc((void**)&c->sched, sizeof(unsigned int) * (1 + c->nxl)));
             RF_CUDA(cudaMemsetAsync(c->sched, 0, sizeof(unsigned int) * (1 + c->nxl), c->stream));
             f.ticket = c->sched;
@@ -968,9 +898,7 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
               f.k3.partials = c->partials;
             }
             mark(c, 2);
-            if constexpr (NN <= 1024)
-              e = c->fuse_q ? PipeLaunch<NN>::k23q(c->nz, min, mout, f, grid, c->stream)
-                            : PipeLaunch<NN>::k23p(c->nz, min, mout, f, grid, c->stream);
+            if constexpr (NN <= 1024) e = PipeLaunch<NN>::k23q(c->nz, min, mout, f, grid, c->stream);
             mark(c, 3);
             mark(c, 4);
             mark(c, 5);

@@ -23,28 +23,108 @@ struct alignas(2 * sizeof(T)) cpx {
   T x, y;
 };
 
+// Packed single precision (sm_100 add/mul/fma.f32x2 -> SASS FADD2 / FMUL2 / FFMA2): a cpx<float>
+// is one 64-bit register pair, a complex add is ONE instruction and a complex multiply TWO.
+// ptxas folds lane swaps, per-lane signs and scalar broadcasts into operand modifiers
+// (R.F32x2.LO_HI.NP, R.F32), so the helpers below are written with plain float2 constructors.
+// Each lane is an IEEE round-to-nearest operation: results do not depend on which kernel
+// (fused or separate passes, one GPU or several) evaluates them.  RF_NO_F32X2 restores the
+// scalar forms (A/B builds).
+#if defined(__CUDA_ARCH__) && !defined(RF_NO_F32X2)
+#define RF_PK 1
+#else
+#define RF_PK 0
+#endif
+
+__host__ __device__ __forceinline__ cpx<float> pk_add(float ax, float ay, float bx, float by) {
+#if RF_PK
+  const float2 r = __fadd2_rn(make_float2(ax, ay), make_float2(bx, by));
+  return {r.x, r.y};
+#else
+  return {ax + bx, ay + by};
+#endif
+}
+__host__ __device__ __forceinline__ cpx<float> pk_mul(float ax, float ay, float bx, float by) {
+#if RF_PK
+  const float2 r = __fmul2_rn(make_float2(ax, ay), make_float2(bx, by));
+  return {r.x, r.y};
+#else
+  return {ax * bx, ay * by};
+#endif
+}
+__host__ __device__ __forceinline__ cpx<float> pk_fma(float ax, float ay, float bx, float by, float cx, float cy) {
+#if RF_PK
+  const float2 r = __ffma2_rn(make_float2(ax, ay), make_float2(bx, by), make_float2(cx, cy));
+  return {r.x, r.y};
+#elif defined(__CUDA_ARCH__)
+  return {__fmaf_rn(ax, bx, cx), __fmaf_rn(ay, by, cy)};
+#else
+  return {ax * bx + cx, ay * by + cy};
+#endif
+}
+__host__ __device__ __forceinline__ cpx<double> pk_add(double ax, double ay, double bx, double by) {
+  return {ax + bx, ay + by};
+}
+__host__ __device__ __forceinline__ cpx<double> pk_mul(double ax, double ay, double bx, double by) {
+  return {ax * bx, ay * by};
+}
+
 template <typename T>
 __host__ __device__ __forceinline__ cpx<T> operator+(cpx<T> a, cpx<T> b) {
-  return {a.x + b.x, a.y + b.y};
+  return pk_add(a.x, a.y, b.x, b.y);
 }
 template <typename T>
 __host__ __device__ __forceinline__ cpx<T> operator-(cpx<T> a, cpx<T> b) {
-  return {a.x - b.x, a.y - b.y};
+  return pk_add(a.x, a.y, -b.x, -b.y);
 }
-// The float form pins which product is fused into the FMA: left to the compiler the choice
-// differs from kernel to kernel, and the field must be bit-identical whichever kernels
-// (fused or separate passes, one GPU or several) produce it.
+// a * b = (a.x b.x - a.y b.y, a.y b.x + a.x b.y).  The float form pins the rounding sequence --
+// t = (a.x b.x, a.y b.x) rounded, then one fused multiply-add per lane -- because the field
+// must be bit-identical whichever kernels (fused or separate passes, one GPU or several)
+// produce it; left to the compiler the choice of the fused product differs from kernel to kernel.
 template <typename T>
 __host__ __device__ __forceinline__ cpx<T> cmul(cpx<T> a, cpx<T> b) {
 #ifdef __CUDA_ARCH__
-  if constexpr (sizeof(T) == 4)
-    return {__fmaf_rn(a.x, b.x, -__fmul_rn(a.y, b.y)), __fmaf_rn(a.x, b.y, __fmul_rn(a.y, b.x))};
+  if constexpr (sizeof(T) == 4) {
+    const cpx<float> t = pk_mul(a.x, a.y, b.x, b.x);
+    return pk_fma(a.y, a.x, -b.y, b.y, t.x, t.y);
+  }
 #endif
   return {a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x};
 }
 template <typename T>
 __host__ __device__ __forceinline__ cpx<T> cconj(cpx<T> a) {
   return {a.x, -a.y};
+}
+// a + i*b and a - i*b
+template <typename T>
+__host__ __device__ __forceinline__ cpx<T> add_i(cpx<T> a, cpx<T> b) {
+  return pk_add(a.x, a.y, -b.y, b.x);
+}
+template <typename T>
+__host__ __device__ __forceinline__ cpx<T> sub_i(cpx<T> a, cpx<T> b) {
+  return pk_add(a.x, a.y, b.y, -b.x);
+}
+
+// c2r along the contiguous axis, Hermitian unpack of the pair (k, H-k) of a half-length line:
+// a = X[k], c = X[H-k], w = exp(+2 pi i k / N); zk = E[k] + i O[k], zh = the same for H-k.
+template <typename T>
+__host__ __device__ __forceinline__ void c2r_unpack_pair(cpx<T> a, cpx<T> c, cpx<T> w, cpx<T>& zk, cpx<T>& zh) {
+  const cpx<T> e = pk_add(a.x, a.y, c.x, -c.y);   // X[k] + conj(X[H-k])
+  const cpx<T> d = pk_add(a.x, a.y, -c.x, c.y);   // X[k] - conj(X[H-k])
+  const cpx<T> o = cmul(d, w);
+  zk = pk_add(e.x, e.y, -o.y, o.x);
+  zh = pk_add(e.x, -e.y, o.y, o.x);
+}
+// k = 0 and k = H/2 of the same unpack (X[0] = P0 + i PN holds two real values, w = i at H/2)
+template <typename T>
+__host__ __device__ __forceinline__ void c2r_unpack_ends(cpx<T> a, cpx<T> m, cpx<T>& z0, cpx<T>& zm) {
+  z0 = pk_add(a.x, a.x, a.y, -a.y);
+  zm = pk_mul(m.x, m.y, (T)2, (T)-2);
+}
+// running (sum, sum of squares) of a real field held as complex pairs: acc1 += x, acc2 += x*x per lane
+__host__ __device__ __forceinline__ void stats_accum(cpx<float> x, cpx<float>& acc1, cpx<float>& acc2) {
+  acc1 = pk_add(acc1.x, acc1.y, x.x, x.y);
+  acc2 = pk_fma(x.x, x.y, x.x, x.y, acc2.x, acc2.y);
 }
 
 // ----------------------------------------------------------------------------------------
@@ -100,14 +180,18 @@ __device__ __forceinline__ cpx<T> mul_tw32(cpx<T> d) {
     constexpr T sn0 = (k == 4 || k == 12) ? (T)1 : (T)-1;         // sign of sin(+)
     constexpr T sn = INV ? sn0 : -sn0;
     // (cs + i sn) * (x + i y) * s = (cs x - sn y) + i (cs y + sn x)
-    return {(cs * d.x - sn * d.y) * s, (cs * d.y + sn * d.x) * s};
+    const cpx<T> u = pk_add(cs * d.x, cs * d.y, -sn * d.y, sn * d.x);
+    return pk_mul(u.x, u.y, s, s);
   } else {
     constexpr T c = (T)rf_cos32(k);
     constexpr T s = (T)(INV ? rf_sin32(k) : -rf_sin32(k));
-    if constexpr (sizeof(T) == 4)
-      return {__fmaf_rn(d.x, c, -__fmul_rn(d.y, s)), __fmaf_rn(d.x, s, __fmul_rn(d.y, c))};
-    else
+    if constexpr (sizeof(T) == 4) {
+      // same rounding sequence as cmul(d, {c, s})
+      const cpx<float> t = pk_mul(d.x, d.y, c, c);
+      return pk_fma(d.y, d.x, -s, s, t.x, t.y);
+    } else {
       return {d.x * c - d.y * s, d.x * s + d.y * c};
+    }
   }
 }
 
@@ -146,8 +230,11 @@ __device__ __forceinline__ void fft_dif(cpx<T> (&v)[R]) {
 }
 
 // ----------------------------------------------------------------------------------------
-// Philox4x32-10 (Salmon et al. 2011).  Counter = 128 bit, key = 64 bit.
+// Philox4x32-R (Salmon et al. 2011).  Counter = 128 bit, key = 64 bit.  R = RF_PHILOX_ROUNDS.
 // ----------------------------------------------------------------------------------------
+#ifndef RF_PHILOX_ROUNDS
+#define RF_PHILOX_ROUNDS 10
+#endif
 struct philox_out {
   uint32_t w[4];
 };
@@ -158,7 +245,7 @@ __host__ __device__ __forceinline__ philox_out philox4x32_10(uint32_t c0, uint32
   constexpr uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
   constexpr uint32_t W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
 #pragma unroll
-  for (int r = 0; r < 10; ++r) {
+  for (int r = 0; r < RF_PHILOX_ROUNDS; ++r) {
     uint64_t p0 = (uint64_t)M0 * c0;
     uint64_t p1 = (uint64_t)M1 * c2;
     uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
@@ -200,7 +287,7 @@ __device__ __forceinline__ cpx<float> box_muller<float>(uint32_t wa, uint32_t wb
   float ang = (float)(int32_t)wb * 1.4629180792671596e-9f;  // pi / 2^31
   float s, c;
   __sincosf(ang, &s, &c);
-  return {r * c, r * s};
+  return pk_mul(c, s, r, r);
 }
 
 template <>
@@ -400,7 +487,7 @@ __device__ __forceinline__ cpx<T> raw_mode(const ModeGeom<T>& g, const SigmaTabl
   uint64_t q = ((uint64_t)px * g.ny + iy) * nzh + iz;
   philox_out o = philox4x32_10((uint32_t)q, (uint32_t)(q >> 32), 0u, 0u, g.key0, g.key1);
   cpx<T> n = (ix >= hx) ? box_muller<T>(o.w[2], o.w[3]) : box_muller<T>(o.w[0], o.w[1]);
-  return {sig * n.x, sig * n.y};
+  return pk_mul(n.x, n.y, sig, sig);
 }
 
 // symmetrised mode in the public (nx, ny, nz/2+1) layout

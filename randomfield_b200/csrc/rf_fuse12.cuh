@@ -178,8 +178,8 @@ k12_generate_xyfft(const __grid_constant__ pipe::K1PMaps maps, const __grid_cons
           philox_out o = philox4x32_10((uint32_t)q, (uint32_t)(q >> 32), 0u, 0u, g.key0, g.key1);
           cpx<float> n1 = box_muller<float>(o.w[0], o.w[1]);
           cpx<float> n2 = box_muller<float>(o.w[2], o.w[3]);
-          v[m] = {s1 * n1.x, s1 * n1.y};
-          v[m + R1 / 2] = {s2 * n2.x, s2 * n2.y};
+          v[m] = pk_mul(n1.x, n1.y, s1, s1);
+          v[m + R1 / 2] = pk_mul(n2.x, n2.y, s2, s2);
         });
       }
       fft_dif<R1, true>(v);

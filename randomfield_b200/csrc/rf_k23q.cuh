@@ -267,10 +267,10 @@ k23q_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant_
         twu[q] = ld_cpx(twNs + (tid + q * kConsumers) % (P3::H / 2));
       });
       load_step_twiddles_smem<P3::R1>(twr, twHs, tid % P3::M);
-      float a1 = 0.f, a2 = 0.f;
+      cpx<float> a1 = {0.f, 0.f}, a2 = {0.f, 0.f};
       k3q_tile_body<NZ>(B, tid, twr, twu, zs, a1, a2, p.k3.twH);
-      s1 += (double)a1;
-      s2 += (double)a2;
+      s1 += (double)a1.x + (double)a1.y;
+      s2 += (double)a2.x + (double)a2.y;
     }
     fence_proxy_async();
     mbar_arrive(&done[b]);

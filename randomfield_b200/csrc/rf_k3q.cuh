@@ -23,7 +23,7 @@ template <int NZ>
 __device__ __forceinline__ void k3q_tile_body(cpx<float>* __restrict__ B, int tid,
                                               const cpx<float> (&twr)[LPlan<NZ>::R1],
                                               const cpx<float> (&twu)[K3Consts<NZ>::kPairsPerThread],
-                                              const float* zs, float& a1, float& a2, const cpx<float>* twH) {
+                                              const float* zs, cpx<float>& a1, cpx<float>& a2, const cpx<float>* twH) {
   using P = LPlan<NZ>;
   constexpr int H = P::H, HE = P::HE, R1 = P::R1, R2 = HE / R1, M = P::M;
   constexpr int kPairsPerThread = K3Consts<NZ>::kPairsPerThread;
@@ -41,15 +41,10 @@ __device__ __forceinline__ void k3q_tile_body(cpx<float>* __restrict__ B, int ti
         const int k = tid + q * kConsumers;
         if (q == 0 && k == 0) {
           cpx<float> a = Lp[0], m = Lp[H / 2];
-          Lp[0] = {a.x + a.y, a.x - a.y};
-          Lp[H / 2] = {2.f * m.x, -2.f * m.y};
+          c2r_unpack_ends(a, m, Lp[0], Lp[H / 2]);
         } else {
           cpx<float> a = Lp[k], c = Lp[H - k];
-          cpx<float> e = {a.x + c.x, a.y - c.y};
-          cpx<float> d = {a.x - c.x, a.y + c.y};
-          cpx<float> o = cmul(d, twu[q]);
-          Lp[k] = {e.x - o.y, e.y + o.x};
-          Lp[H - k] = {e.x + o.y, o.x - e.y};
+          c2r_unpack_pair(a, c, twu[q], Lp[k], Lp[H - k]);
         }
       });
     }
@@ -60,15 +55,10 @@ __device__ __forceinline__ void k3q_tile_body(cpx<float>* __restrict__ B, int ti
       cpx<float>* Lp = B + l * H;
       if (k == 0) {
         cpx<float> a = Lp[0], m = Lp[H / 2];
-        Lp[0] = {a.x + a.y, a.x - a.y};
-        Lp[H / 2] = {2.f * m.x, -2.f * m.y};
+        c2r_unpack_ends(a, m, Lp[0], Lp[H / 2]);
       } else {
         cpx<float> a = Lp[k], c = Lp[H - k];
-        cpx<float> e = {a.x + c.x, a.y - c.y};
-        cpx<float> d = {a.x - c.x, a.y + c.y};
-        cpx<float> o = cmul(d, twu[0]);
-        Lp[k] = {e.x - o.y, e.y + o.x};
-        Lp[H - k] = {e.x + o.y, o.x - e.y};
+        c2r_unpack_pair(a, c, twu[0], Lp[k], Lp[H - k]);
       }
     }
   }
@@ -137,14 +127,12 @@ __device__ __forceinline__ void k3q_tile_body(cpx<float>* __restrict__ B, int ti
       constexpr int k2 = decltype(ki)::value;
       cpx<float> x = u[q][brev<R2>(k2)];
       const int k = k1 + R1 * k2;
-      a1 += x.x + x.y;
-      a2 = fmaf(x.x, x.x, fmaf(x.y, x.y, a2));
+      stats_accum(x, a1, a2);
       const int pos = P::SPLIT == 1 ? k : P::SPLIT * k + (l % P::SPLIT);
       const int line = l / P::SPLIT;
       if (zs) {
         float2 z = __ldg(reinterpret_cast<const float2*>(zs) + pos);
-        x.x *= z.x;
-        x.y *= z.y;
+        x = pk_mul(x.x, x.y, z.x, z.y);
       }
       st_cpx(B + line * H + pos, x);
     });
@@ -213,10 +201,10 @@ __global__ void __launch_bounds__(kThreads, 1) k3q_c2r_lines(const K3PParams p) 
   for (int t = first; t < p.ntiles; t += step) {
     cpx<float>* const B = buf0 + b * kBufElems;
     mbar_wait(&full[b], ph);
-    float a1 = 0.f, a2 = 0.f;
+    cpx<float> a1 = {0.f, 0.f}, a2 = {0.f, 0.f};
     k3q_tile_body<NZ>(B, tid, twr, twu, zs, a1, a2, p.twH);
-    s1 += (double)a1;
-    s2 += (double)a2;
+    s1 += (double)a1.x + (double)a1.y;
+    s2 += (double)a2.x + (double)a2.y;
     fence_proxy_async();
     mbar_arrive(&done[b]);
     if (++b == 3) { b = 0; ph ^= 1; }

@@ -45,7 +45,8 @@ __device__ __forceinline__ double warp_excl_scan(double v, int lane) {
   return incl - v;
 }
 
-// field: [nlines][nz] real, psi overwrites dPhi.  blockDim.x = 32 * warps; dynamic shared
+// field: [nlines][nz] real dPhi; psi goes to `out` (same layout; may alias field: every read of a
+// line precedes its writes).  blockDim.x = 32 * warps; dynamic shared
 // memory: 5 * (nz + 32) doubles (the coefficient tables, in the same blocked + padded layout as
 // the lines: a lane reads its own block's coefficients without touching global memory) followed
 // by warps * (nz + 32) * sizeof(T).
@@ -53,7 +54,7 @@ __host__ __device__ inline size_t lens_smem_bytes(int nz, int warps, size_t elem
   return (size_t)5 * (nz + 32) * sizeof(double) + (size_t)warps * (nz + 32) * elem;
 }
 template <typename T>
-__global__ void lensing_scan_kernel(T* __restrict__ field, long long nlines, int nz, int i_min, LensTables tb) {
+__global__ void lensing_scan_kernel(const T* field, T* out, long long nlines, int nz, int i_min, LensTables tb) {
   extern __shared__ __align__(16) unsigned char lens_smem[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int lb = (nz + 31) / 32;                      // samples per lane block
@@ -79,7 +80,8 @@ __global__ void lensing_scan_kernel(T* __restrict__ field, long long nlines, int
 
   for (long long line = (long long)blockIdx.x * nwarps + wid; line < nlines;
        line += (long long)gridDim.x * nwarps) {
-    T* const gl = field + line * nz;
+    const T* const gl = field + line * nz;
+    T* const ol = out + line * nz;
     // stage the line: 16 independent loads in flight per lane before the first shared store
     for (int k0 = lane; k0 < nz; k0 += 32 * 16) {
       T r[16];
@@ -151,7 +153,7 @@ __global__ void lensing_scan_kernel(T* __restrict__ field, long long nlines, int
       f2 = f1; f1 = f0; g2 = g1; g1 = g0;
     }
     __syncwarp();
-    for (int k = lane; k < nz; k += 32) gl[k] = at(k);
+    for (int k = lane; k < nz; k += 32) ol[k] = at(k);
     __syncwarp();
   }
 }
@@ -208,7 +210,7 @@ template <> struct LVec<double> {
 };
 
 template <typename T, int TPB, int S, bool P>
-__device__ __forceinline__ void lens4_body(T* __restrict__ field, long long nlines, int nz, int i_min,
+__device__ __forceinline__ void lens4_body(const T* field, T* out, long long nlines, int nz, int i_min,
                                            const LensTables& tb, double* tot) {
   constexpr int W = TPB / 32, V = S / 4;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -244,7 +246,8 @@ __device__ __forceinline__ void lens4_body(T* __restrict__ field, long long nlin
   // iterations of the CTA (uniform: barriers inside) and of this thread's line group
   const int nit = base0 < nlines ? (int)((nlines - 1 - base0) / lstride) + 1 : 0;
   const int my_nit = line0 < nlines ? (int)((nlines - 1 - line0) / lstride) + 1 : 0;
-  T* gp = field + line0 * nz + j0;
+  const T* gp = field + line0 * nz + j0;
+  T* op = out + line0 * nz + j0;
   const long long gstep = lstride * nz;
   LVec<T> cur[V];
   T nb2 = 0, nb3 = 0;
@@ -257,7 +260,7 @@ __device__ __forceinline__ void lens4_body(T* __restrict__ field, long long nlin
   };
   fetch(gp, my_nit > 0);
   int buf = 0;
-  for (int it = 0; it < nit; ++it, buf ^= 1, gp += gstep) {
+  for (int it = 0; it < nit; ++it, buf ^= 1, gp += gstep, op += gstep) {
     T f[S];
 #pragma unroll
     for (int s = 0; s < S; ++s) f[s] = cur[s >> 2].v[s & 3];
@@ -329,7 +332,7 @@ __device__ __forceinline__ void lens4_body(T* __restrict__ field, long long nlin
     }
     if (it < my_nit) {
 #pragma unroll
-      for (int v = 0; v < V; ++v) LVec<T>::store(gp + 4 * v, psi[4 * v], psi[4 * v + 1], psi[4 * v + 2], psi[4 * v + 3]);
+      for (int v = 0; v < V; ++v) LVec<T>::store(op + 4 * v, psi[4 * v], psi[4 * v + 1], psi[4 * v + 2], psi[4 * v + 3]);
     }
   }
 }
@@ -341,10 +344,10 @@ template <typename T, int S> struct LensOcc { static constexpr int value = (size
 template <typename T> struct LensS { static constexpr int value = sizeof(T) == 4 ? 8 : 4; };
 template <typename T, int TPB, int S>
 __global__ void __launch_bounds__(TPB, LensOcc<T, S>::value / TPB)
-lensing_scan4_kernel(T* __restrict__ field, long long nlines, int nz, int i_min, LensTables tb) {
+lensing_scan4_kernel(const T* field, T* out, long long nlines, int nz, int i_min, LensTables tb) {
   __shared__ __align__(16) double tot[2 * (TPB / 32) * 4];
-  if (i_min & 1) lens4_body<T, TPB, S, true>(field, nlines, nz, i_min, tb, tot);
-  else lens4_body<T, TPB, S, false>(field, nlines, nz, i_min, tb, tot);
+  if (i_min & 1) lens4_body<T, TPB, S, true>(field, out, nlines, nz, i_min, tb, tot);
+  else lens4_body<T, TPB, S, false>(field, out, nlines, nz, i_min, tb, tot);
 }
 
 // whole warps per line and whole lines per CTA: nz / S a power of two in [32, 512]

@@ -261,7 +261,7 @@ template <int NZ>
 __device__ __forceinline__ void k3_tile_body(cpx<float>* __restrict__ D, cpx<float>* __restrict__ work, int tid,
                                              const cpx<float> (&twr)[LPlan<NZ>::R1],
                                              const cpx<float> (&twu)[K3Consts<NZ>::kPairsPerThread],
-                                             const float* zs, float& a1, float& a2,
+                                             const float* zs, cpx<float>& a1, cpx<float>& a2,
                                              const cpx<float>* twH = nullptr) {
   using P = LPlan<NZ>;
   constexpr int H = P::H;
@@ -280,15 +280,10 @@ __device__ __forceinline__ void k3_tile_body(cpx<float>* __restrict__ D, cpx<flo
           const int k = tid + q * kConsumers;
           if (q == 0 && k == 0) {
             cpx<float> a = Lp[0], m = Lp[H / 2];
-            Lp[0] = {a.x + a.y, a.x - a.y};          // X[0], X[H] are real
-            Lp[H / 2] = {2.f * m.x, -2.f * m.y};
+            c2r_unpack_ends(a, m, Lp[0], Lp[H / 2]);
           } else {
             cpx<float> a = Lp[k], c = Lp[H - k];
-            cpx<float> e = {a.x + c.x, a.y - c.y};   // X[k] + conj(X[H-k])
-            cpx<float> d = {a.x - c.x, a.y + c.y};   // X[k] - conj(X[H-k])
-            cpx<float> o = cmul(d, twu[q]);          // * exp(+2 pi i k / NZ)
-            Lp[k] = {e.x - o.y, e.y + o.x};
-            Lp[H - k] = {e.x + o.y, o.x - e.y};
+            c2r_unpack_pair(a, c, twu[q], Lp[k], Lp[H - k]);
           }
         });
       }
@@ -300,15 +295,10 @@ __device__ __forceinline__ void k3_tile_body(cpx<float>* __restrict__ D, cpx<flo
         cpx<float>* Lp = D + l * H;
         if (k == 0) {
           cpx<float> a = Lp[0], m = Lp[H / 2];
-          Lp[0] = {a.x + a.y, a.x - a.y};
-          Lp[H / 2] = {2.f * m.x, -2.f * m.y};
+          c2r_unpack_ends(a, m, Lp[0], Lp[H / 2]);
         } else {
           cpx<float> a = Lp[k], c = Lp[H - k];
-          cpx<float> e = {a.x + c.x, a.y - c.y};
-          cpx<float> d = {a.x - c.x, a.y + c.y};
-          cpx<float> o = cmul(d, twu[0]);
-          Lp[k] = {e.x - o.y, e.y + o.x};
-          Lp[H - k] = {e.x + o.y, o.x - e.y};
+          c2r_unpack_pair(a, c, twu[0], Lp[k], Lp[H - k]);
         }
       }
     }
@@ -337,15 +327,13 @@ __device__ __forceinline__ void k3_tile_body(cpx<float>* __restrict__ D, cpx<flo
     });
     ConsumerSync()();
     step_b<HE, P::R1, L>(work, tid, P::TE, [&](int k, int l, cpx<float> x) {
-      a1 += x.x + x.y;
-      a2 = fmaf(x.x, x.x, fmaf(x.y, x.y, a2));
+      stats_accum(x, a1, a2);
       // engine line l = SPLIT*line + parity holds outputs parity, parity + SPLIT, ...
       const int pos = P::SPLIT == 1 ? k : P::SPLIT * k + (l % P::SPLIT);
       const int line = l / P::SPLIT;
       if (zs) {
         float2 z = __ldg(reinterpret_cast<const float2*>(zs) + pos);
-        x.x *= z.x;
-        x.y *= z.y;
+        x = pk_mul(x.x, x.y, z.x, z.y);
       }
       st_cpx(D + line * H + pos, x);
     });
@@ -434,10 +422,10 @@ __global__ void __launch_bounds__(kThreads, 1) k3p_c2r_lines(const K3PParams p) 
     cpx<float>* const D = dense0 + b * kDenseElems;
     mbar_wait(&full[b], (i >> 1) & 1);
 
-    float a1 = 0.f, a2 = 0.f;
+    cpx<float> a1 = {0.f, 0.f}, a2 = {0.f, 0.f};
     k3_tile_body<NZ>(D, work, tid, twr, twu, zs, a1, a2, p.twH);
-    s1 += (double)a1;
-    s2 += (double)a2;
+    s1 += (double)a1.x + (double)a1.y;
+    s2 += (double)a2.x + (double)a2.y;
     fence_proxy_async();
     mbar_arrive(&done[b]);
   }
@@ -689,8 +677,8 @@ k1p_generate_xfft(const __grid_constant__ K1PMaps maps, const K1PParams p) {
           philox_out o = philox4x32_10((uint32_t)q, (uint32_t)(q >> 32), 0u, 0u, g.key0, g.key1);
           cpx<float> n1 = box_muller<float>(o.w[0], o.w[1]);
           cpx<float> n2 = box_muller<float>(o.w[2], o.w[3]);
-          v[m] = {s1 * n1.x, s1 * n1.y};
-          v[m + P::R1 / 2] = {s2 * n2.x, s2 * n2.y};
+          v[m] = pk_mul(n1.x, n1.y, s1, s1);
+          v[m + P::R1 / 2] = pk_mul(n2.x, n2.y, s2, s2);
         });
       }
     });
@@ -802,8 +790,8 @@ k1q_generate_xfft(const __grid_constant__ K1PMaps maps, const K1PParams p) {
         philox_out o = philox4x32_10((uint32_t)q, (uint32_t)(q >> 32), 0u, 0u, g.key0, g.key1);
         cpx<float> n1 = box_muller<float>(o.w[0], o.w[1]);
         cpx<float> n2 = box_muller<float>(o.w[2], o.w[3]);
-        v[m] = {s1 * n1.x, s1 * n1.y};
-        v[m + R1 / 2] = {s2 * n2.x, s2 * n2.y};
+        v[m] = pk_mul(n1.x, n1.y, s1, s1);
+        v[m + R1 / 2] = pk_mul(n2.x, n2.y, s2, s2);
       });
     }
     fft_dif<R1, true>(v);
@@ -1086,10 +1074,10 @@ k23p_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant_
         twu[q] = ld_cpx(twNs + (tid + q * kConsumers) % (P3::H / 2));
       });
       load_step_twiddles_smem<P3::R1>(twr, twHs, tid % P3::M);   // (NZ <= 2048 here: SPLIT == 1)
-      float a1 = 0.f, a2 = 0.f;
+      cpx<float> a1 = {0.f, 0.f}, a2 = {0.f, 0.f};
       k3_tile_body<NZ>(D, work, tid, twr, twu, zs, a1, a2, p.k3.twH);
-      s1 += (double)a1;
-      s2 += (double)a2;
+      s1 += (double)a1.x + (double)a1.y;
+      s2 += (double)a2.x + (double)a2.y;
     }
     fence_proxy_async();
     mbar_arrive(&done[b]);
