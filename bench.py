@@ -40,19 +40,6 @@ PASS_NAMES = ("k1_generate_xfft", "k2_strided_fft", "k3_c2r_lines")
 PIPE_NAMES = ("k1p_generate_xfft", "k2p_strided_fft", "k3p_c2r_lines")
 
 
-def kernel_names(grid, pipelined):
-    """Names of the three pass kernels the library launches for this grid (rf_api.cu dispatch)."""
-    if not pipelined:
-        return PASS_NAMES
-    k1q = os.environ.get("RF_K1Q", "1") != "0"
-    big = os.environ.get("RF_BIG", "1") != "0"
-    k1 = ("k1q_generate_xfft" if k1q else "k1p_generate_xfft") if grid[0] <= 1024 else (
-        "k1b_generate_xfft" if big else PASS_NAMES[0])
-    k2 = "k2p_strided_fft" if grid[1] <= 1024 else ("k2b_strided_fft" if big else PASS_NAMES[1])
-    k3 = "k3q_c2r_lines" if (os.environ.get("RF_K3Q", "1") != "0" and grid[2] >= 128) else "k3p_c2r_lines"
-    return (k1, k2, k3)
-
-
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -111,38 +98,63 @@ class ClockSampler(object):
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+CPU_SAMPLE_N = 512      # cube edge of the bounded CPU sample (one step = one 512^3 field, about 5-9 s)
+
+
 def cpu_reference_step(n, seed):
-    """One pass of the reference algorithm (generate.py:191-219) on the host: the numpy
-    restatement in oracle/oracle.py, bit-identical to the reference modules.  Returns seconds."""
+    """One pass of the reference's CPU implementation of the path (generate.py:191-219) on an
+    n^3 grid.  Runs the UNMODIFIED reference modules (oracle/ref_replay.py: from /root/reference,
+    or from the byte-for-byte copy oracle/make_ref.py staged under oracle/_ref/) when they are
+    present, else the numpy restatement oracle/oracle.py, which is bit-identical to them
+    (tests/test_oracle.py).  Returns (seconds, kind)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
-    import oracle
-    power = oracle.load_default_power()
-    t0 = time.perf_counter()
-    r = oracle.generate_delta_field((n, n, n), SPACING, power, seed=seed, save_potential=False)
-    dt = time.perf_counter() - t0
+    import ref_replay
+    if ref_replay.available():
+        t0 = time.perf_counter()
+        r = ref_replay.replay(n, n, n, SPACING, seed=seed, save_potential=False)
+        dt = time.perf_counter() - t0
+        kind = "reference"
+    else:
+        import oracle
+        power = oracle.load_default_power()
+        t0 = time.perf_counter()
+        r = oracle.generate_delta_field((n, n, n), SPACING, power, seed=seed, save_potential=False)
+        dt = time.perf_counter() - t0
+        kind = "port"
     assert np.isfinite(r["rms"])
-    return dt
+    return dt, kind
+
+
+def cpu_sample_text(n, grid, kind):
+    return ("%d^3 sub-grid of the %s workload per step; %s; numpy pocketfft irfftn + MT19937 normal, "
+            "single-threaded like the reference (transform.py:258-260 builds its plans with threads=1)"
+            % (n, "x".join(map(str, grid)),
+               "unmodified reference modules transform.py / powertools.py / random.py replayed as "
+               "generate.py:191-219 calls them" if kind == "reference" else "numpy restatement oracle/oracle.py"))
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    n = args.cpu_n or 256
+    n = args.cpu_n or CPU_SAMPLE_N
+    grid = parse_grid(args)
+    kind = "port"
     for w in range(args.warmup):
-        cpu_reference_step(n, 1000 + w)
-    times = [cpu_reference_step(n, 123 + s) for s in range(args.steps)]
+        _, kind = cpu_reference_step(min(n, 128), 1000 + w)     # warm-up: imports, table load, page faults
+    times = []
+    for s in range(args.steps):
+        dt, kind = cpu_reference_step(n, 123 + s)
+        times.append(dt)
     total = float(np.sum(times))
     value = args.steps * n ** 3 / total / 1e6
-    grid = parse_grid(args)
-    sample = "%d^3 grid per step (bounded sample of the %s workload), numpy pocketfft + MT19937" % (
-        n, "x".join(map(str, grid)))
+    sample = cpu_sample_text(n, grid, kind)
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic", "config": {"workload": workload_name(grid, args.gpus), "cpu_sample": sample},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
+        "data": "synthetic", "config": workload_config(grid, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -164,6 +176,160 @@ def parse_grid(args):
 def workload_name(grid, gpus):
     return "seed->delta(x) %dx%dx%d f32, spacing %.1f Mpc/h, bundled P(k), %d GPU(s)" % (
         grid[0], grid[1], grid[2], SPACING, gpus)
+
+
+def exchange_mode(world):
+    """The exchange SlabEngine selects from the environment (slab.py), without creating one."""
+    if world < 2:
+        return "single"
+    mode = os.environ.get("RF_EXCHANGE", "")
+    if not mode:
+        mode = "direct" if os.environ.get("RF_DIRECT") == "1" else (
+            "nccl" if os.environ.get("RF_DIRECT") == "0" else "chunked")
+    return mode
+
+
+def workload_config(grid, world, mode=None):
+    """`config` of the JSON line: identical in the GPU arm and in the reference arm."""
+    mode = mode or exchange_mode(world)
+    local = float(grid[0]) * grid[1] * grid[2] / world
+    par = "single GPU" if world == 1 else "y-slab k-space -> %s -> x-slab real space" % {
+        "direct": "pass-1 stores into peer receive buffers over NVLink (no separate all-to-all)",
+        "chunked": "copy-engine pushes into peer receive buffers, pipelined with passes 1 and 2 over chunks "
+                   "of z columns",
+        "nccl": "NCCL all-to-all"}.get(mode, mode)
+    return {"workload": workload_name(grid, world), "grid": list(grid),
+            "l2": "working set %.1f GB per GPU >> 126 MB L2, no flush needed" % (4 * local / 1e9),
+            "parallelism": par}
+
+
+def cufft_c2r_ms(grid, stream, reps=5):
+    """Comparison point only (north_star: "cuFFT ... is timed only as a comparison point, never as
+    the product"): one in-place 3-D C2R cuFFT transform of the same half-complex grid, CUDA-event
+    timed on `stream`.  libcufft is loaded with ctypes here; librf_b200.so never links it."""
+    import ctypes
+    import glob
+    import torch
+    cands = []
+    for base in sys.path + [os.path.dirname(torch.__file__) + "/.."]:
+        cands += glob.glob(os.path.join(base, "nvidia", "cufft", "lib", "libcufft.so.*"))
+    cands += ["libcufft.so.11", "libcufft.so"]
+    lib = None
+    for c in cands:
+        try:
+            lib = ctypes.CDLL(c)
+            break
+        except OSError:
+            continue
+    if lib is None:
+        return None
+    nx, ny, nz = grid
+    plan = ctypes.c_int()
+    CUFFT_C2R = 0x2c
+    ws = ctypes.c_size_t()
+    if lib.cufftCreate(ctypes.byref(plan)) != 0:
+        return None
+    try:
+        lib.cufftSetStream(plan, ctypes.c_void_p(stream.cuda_stream))
+        if lib.cufftMakePlan3d(plan, nx, ny, nz, CUFFT_C2R, ctypes.byref(ws)) != 0:
+            return None
+        buf = torch.empty(nx * ny * (nz // 2 + 1) * 2, dtype=torch.float32, device="cuda")
+        buf.normal_()
+        ptr = ctypes.c_void_p(buf.data_ptr())
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            stream.wait_stream(torch.cuda.current_stream())
+            for _ in range(2):
+                lib.cufftExecC2R(plan, ptr, ptr)
+            e0.record(stream)
+            for _ in range(reps):
+                if lib.cufftExecC2R(plan, ptr, ptr) != 0:
+                    return None
+            e1.record(stream)
+        stream.synchronize()
+        return {"ms": e0.elapsed_time(e1) / reps, "workspace_bytes": int(ws.value),
+                "what": "cufftExecC2R in place on (%d, %d, %d) complex64, plan from cufftMakePlan3d; "
+                        "transform only (no mode generation)" % (nx, ny, nz // 2 + 1)}
+    finally:
+        lib.cufftDestroy(plan)
+
+
+def f64_line(power, stream):
+    """BASELINE config 2 in float64 mode: 256^3 with 4 Mpc/h smoothing, device-timed."""
+    import torch
+    from randomfield_b200 import _lib, powertools
+    n = 256
+    e = _lib.Engine(n, n, n, dtype=np.float64)
+    k, sig = powertools.sigma_table(powertools.filter_power(power, 4.0), (n, n, n), SPACING)
+    e.set_power(k, sig, SPACING)
+    e.set_stream(stream.cuda_stream)
+    for w in range(3):
+        e.generate_delta(w)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 10
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        for r in range(reps):
+            e.generate_delta(100 + r)
+        e1.record(stream)
+    stream.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    names = e.kernel_names
+    e.close()
+    return {"grid": [n, n, n], "dtype": "f64", "smoothing_Mpc_h": 4.0, "ms_per_step": ms,
+            "Mcells_s": n ** 3 / ms / 1e3, "bytes_per_cell": 40, "GB_s": 40.0 * n ** 3 / ms / 1e6,
+            "kernels": list(names)}
+
+
+def check_bit_identity(eng, world, rank, power, stream):
+    """Gate 3 of north_star on the ranks of THIS run: (a) a 512x512x128 grid generated through the
+    same exchange mode as the timed grid, every rank's x-slab compared bit for bit with the
+    single-rank field it computes itself; (b) two steps of the timed grid with the same seed give
+    the same bits (a missed fence would show as a corrupted block).  Returns a dict; all ranks
+    must call it."""
+    import torch
+    import torch.distributed as dist
+    from randomfield_b200 import _lib, powertools
+    from randomfield_b200.slab import SlabEngine
+    out = {}
+    # (b) same seed twice on the timed grid
+    def checksum():
+        f = eng.engine.field_tensor().view(torch.int32)
+        return int(f.to(torch.int64).sum().item()), int((f.to(torch.int64) * 2654435761 % 1000003).sum().item())
+    with torch.cuda.stream(stream):
+        eng.generate(4242)
+        stream.synchronize()
+        c1 = checksum()
+        eng.generate(17)
+        eng.generate(4242)
+        stream.synchronize()
+        c2 = checksum()
+    same = torch.tensor([1 if c1 == c2 else 0], dtype=torch.int64, device="cuda")
+    # (a) small grid, distributed vs single rank
+    small = (512, 512, 128)
+    ok_small = torch.tensor([1], dtype=torch.int64, device="cuda")
+    if world > 1:
+        se = SlabEngine(*small, SPACING, power, dtype=np.float32)
+        se.generate(99)
+        se.stream.synchronize()
+        mine = se.engine.field_tensor().clone()
+        single = _lib.Engine(*small, dtype=np.float32)
+        k, sig = powertools.sigma_table(power, small, SPACING)
+        single.set_power(k, sig, SPACING)
+        single.generate_delta(99)
+        single.sync()
+        nxl = small[0] // world
+        want = single.field_tensor()[rank * nxl:(rank + 1) * nxl]
+        ok_small[0] = 1 if torch.equal(mine.view(torch.int32), want.view(torch.int32)) else 0
+        out["small_grid_mode"] = se.mode
+        single.close()
+        dist.all_reduce(ok_small, op=dist.ReduceOp.MIN)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+    out["bit_identical"] = bool(ok_small.item()) if world > 1 else None
+    out["repeatable"] = bool(same.item())
+    out["what"] = ("512x512x128 through the same exchange: every rank's x-slab == the single-rank field, bit for "
+                   "bit; and two steps of the timed grid with one seed give identical bits")
+    return out
 
 
 def run_ours(args):
@@ -225,8 +391,10 @@ def run_ours(args):
     pass_ms /= nprobe
     clocks = sampler.stop() if rank == 0 else None
     mean, std = eng.global_stats()
-    pipelined = eng.engine.is_pipelined
+    lib_names = eng.engine.kernel_names          # what the library launches for this context
     fused = eng.engine.fused_yz if (world == 1 or eng.mode != "chunked") else 0
+    if not fused and lib_names[1] == "k23q_fused_yz":   # chunked exchange: passes 2 and 3 run separately
+        lib_names = (lib_names[0], "k2p_strided_fft", "k3q_c2r_lines" if grid[2] >= 128 else "k3p_c2r_lines")
     if world > 1:
         t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -264,6 +432,12 @@ def run_ours(args):
                   "lensing_potential_ms": e3.elapsed_time(e4),
                   "bytes_per_cell": {"lognormal_density": 8, "newtonian_potential": 20, "lensing_potential": 8}}
 
+    identity = check_bit_identity(eng, world, rank, power, stream)
+    cufft = f64 = None
+    if world == 1 and not args.quick:
+        cufft = cufft_c2r_ms(grid, stream)
+        f64 = f64_line(power, stream)
+
     # ---- end to end through the public API (N=1: Generator; N>1: slab + host copy) ------
     e2e = None
     if (rank == 0 or world > 1) and not args.no_e2e:
@@ -276,11 +450,11 @@ def run_ours(args):
 
     peak, peak_src = measured_peaks()
     local_cells = cells / world
-    names = kernel_names(grid, pipelined)
+    names = lib_names
     pass_bytes = list(PASS_BYTES_PER_CELL)
     if fused:
         # passes 2 and 3 run as ONE kernel: both passes' algorithmic bytes, one duration
-        names = (names[0], "k23q_fused_yz" if fused == 2 else "k23p_fused_yz")
+        names = (names[0], "k23q_fused_yz")
         pass_ms = np.array([pass_ms[0], pass_ms[1] + pass_ms[2]])
         pass_bytes = [pass_bytes[0], pass_bytes[1] + pass_bytes[2]]
     dom = int(np.argmax(pass_ms))
@@ -311,14 +485,10 @@ def run_ours(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(grid, world), "grid": list(grid),
-                   "l2": "working set %.1f GB per GPU >> 126 MB L2, no flush needed" % (4 * local_cells / 1e9),
-                   "parallelism": ("y-slab k-space -> %s -> x-slab real space" % {
-                       "direct": "pass-1 stores into peer receive buffers over NVLink (no separate all-to-all)",
-                       "chunked": "copy-engine pushes into peer receive buffers, pipelined with passes 1 and 2 "
-                                  "over %d chunks of z columns" % eng.nchunks,
-                       "nccl": "NCCL all-to-all"}.get(eng.mode, eng.mode)) if world > 1 else "single GPU",
-                   "field_std": std, "field_mean": mean},
+        "config": dict(workload_config(grid, world, eng.mode if world > 1 else None),
+                       bit_identical=identity.get("bit_identical"), repeatable=identity["repeatable"]),
+        "field": {"std": std, "mean": mean, "chunks": eng.nchunks},
+        "identity_check": identity,
         "roofline": {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "peak_source": peak_src,
@@ -333,18 +503,24 @@ def run_ours(args):
         "kernels_gbs": dict(zip(names, [float(b * local_cells / (t * 1e-3) / 1e9)
                                         for b, t in zip(pass_bytes, pass_ms)])),
         "config3_addons": extras,
+        "cufft_c2r": cufft,
+        "cufft_note": None if not cufft else (
+            "comparison point only: cuFFT's 3-D C2R of an existing k-field (%.3f ms) beside this path's passes "
+            "2 + 3 (%.3f ms) and the whole seed -> delta(x) step incl. mode generation (%.3f ms)"
+            % (cufft["ms"], float(np.sum(pass_ms[1:])), ms_step)),
+        "config2_f64": f64,
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
     }
     if world > 1:
         nvl_bytes = eng.exchange_bytes
-        line["config"]["all_to_all_bytes_per_gpu"] = nvl_bytes
+        line["field"]["all_to_all_bytes_per_gpu"] = nvl_bytes
     if args.cpu_n != 0 and world == 1:
-        n = args.cpu_n or 512
-        sec = cpu_reference_step(n, 123)
-        line["cpu_baseline"] = {
-            "value": n ** 3 / sec / 1e6, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": "%d^3 grid, one pass of the reference algorithm (oracle port: numpy pocketfft "
-                      "irfftn + MT19937 normal), %.1f s" % (n, sec)}
+        n = args.cpu_n or CPU_SAMPLE_N
+        sec, kind = cpu_reference_step(n, 123)
+        line["cpu_baseline"] = {"value": n ** 3 / sec / 1e6, "unit": UNIT, "cores": 1, "kind": kind,
+                                "sample": cpu_sample_text(n, grid, kind) + "; one step, %.1f s" % sec}
+    if identity.get("bit_identical") is False or not identity["repeatable"]:
+        line["error"] = "bit-identity check failed"
     if getattr(args, "_saved_stdout", None) is not None:
         sys.stdout.flush()
         os.dup2(args._saved_stdout, 1)
@@ -352,7 +528,7 @@ def run_ours(args):
     if world > 1:
         os.dup2(2, 1)
         dist.destroy_process_group()
-    return 0
+    return 1 if "error" in line else 0
 
 
 def run_e2e(args, grid, world, rank, eng, barrier):
@@ -418,6 +594,7 @@ def main():
     ap.add_argument("--cpu-n", type=int, default=None,
                     help="cube size of the CPU baseline sample (0 disables it in the GPU arm)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the end-to-end leg (profiling runs)")
+    ap.add_argument("--quick", action="store_true", help="skip the cuFFT comparison and the float64 line")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

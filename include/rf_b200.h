@@ -26,8 +26,10 @@ typedef struct rf_ctx rf_ctx;
 enum { RF_F32 = 0, RF_F64 = 1 };
 enum { RF_OK = 0, RF_ERR_ARG = -1, RF_ERR_CUDA = -2, RF_ERR_STATE = -3 };
 
-/* which device buffer rf_device_ptr returns */
-enum { RF_BUF_FIELD = 0, RF_BUF_RECV = 1, RF_BUF_PARTIALS = 2 };
+/* which device buffer rf_device_ptr returns.  RF_BUF_AUX is the same memory as RF_BUF_RECV: the
+ * all-to-all receive buffer during a slab-decomposed step, afterwards the second real-space array
+ * (the lensing potential of rf_lensing; scratch of rf_r2c_power) */
+enum { RF_BUF_FIELD = 0, RF_BUF_RECV = 1, RF_BUF_PARTIALS = 2, RF_BUF_AUX = 1 };
 
 const char* rf_last_error(void);
 int rf_version(void);
@@ -53,6 +55,9 @@ int rf_set_power(rf_ctx* ctx, int n, const double* k, const double* sigma, doubl
  * host array of 2*nx*ny*(nz/2+1) doubles in the reference order, uploaded once.
  * NULL clears it and returns to the Philox generator. */
 int rf_set_noise(rf_ctx* ctx, const double* host_noise);
+/* the same array uploaded in slabs of x rows [x0, x1) (host_rows points at row x0), so that the
+ * caller never has to hold 16 bytes per mode on the host (random.py:25-27: "should chunk") */
+int rf_set_noise_rows(rf_ctx* ctx, const double* host_rows, int x0, int x1);
 
 /* Pass 1 of generate_delta_field: fill_with_log10k + tabulate_sigmas + randomize +
  * symmetrize (generate.py:191-199) fused with the axis-0 pass of Plan.execute
@@ -81,6 +86,17 @@ int rf_density(rf_ctx* ctx, int lognormal, double sigma, const double* growth,
 
 /* copy this rank's real field [nx/world][ny][nz] to host memory (synchronous) */
 int rf_copy_field(rf_ctx* ctx, void* host_dst);
+/* Streamed output (the reference hands back views of its one work buffer, generate.py:186-189,
+ * 224-230; here the result has to cross PCIe).  rf_copy_rows copies local x rows [x0, x1) of
+ * RF_BUF_FIELD (the real field) or RF_BUF_AUX (the lensing potential) to host_dst (= address of
+ * row x0) on the context's copy stream, ordered after the work queued so far; async != 0 returns
+ * at once, rf_copy_wait blocks until every queued copy has landed.  host_dst should be page-locked
+ * (rf_host_alloc).  rf_finish_yz_streamed = rf_finish_yz with the output cut into `nranges` ranges
+ * of x rows: pass 2 + pass 3 of range r+1 run while range r crosses PCIe (call rf_copy_wait before
+ * reading host_dst).  Same kernels on the same data: the field is bit-identical to rf_finish_yz. */
+int rf_copy_rows(rf_ctx* ctx, int which, int x0, int x1, void* host_dst, int async);
+int rf_copy_wait(rf_ctx* ctx);
+int rf_finish_yz_streamed(rf_ctx* ctx, const double* zscale, int want_stats, void* host_dst, int nranges);
 /* element count of this rank's real field */
 long long rf_field_elems(rf_ctx* ctx);
 
@@ -148,8 +164,17 @@ int rf_set_direct(rf_ctx* ctx, int enabled);
  * tables5 = 5 contiguous float64 arrays of nz entries built by the caller from DC and cotK:
  *   cotK[j]; a[j], b[j], d[j] = Simpson weights of the three-point panel (j-2, j-1, j) on the
  *   abscissae DC (0 for j < 2); t[j] = (DC[j] - DC[j-1]) / 2 (0 for j = 0).
- * (randomfield_b200.generate.lensing_tables restates the weights of scipy.integrate.simps.) */
+ * (randomfield_b200.generate.lensing_tables restates the weights of scipy.integrate.simps.)
+ * As in the reference (generate.py:398-399) psi is a separate array: it is written to RF_BUF_AUX
+ * and the real-space field stays intact (read it back with rf_copy_rows(ctx, RF_BUF_AUX, ...)). */
 int rf_lensing(rf_ctx* ctx, int i_min, const double* tables5);
+
+/* Power-spectrum estimator: the forward r2c transform the reference plans but never uses
+ * (plan_r2c: generate.py:79-80, transform.py:278-301) of the real-space field, and the mean of
+ * |delta(k)|^2 V / N^6 over the modes of the full k-space whose |k| falls in [k_edges[b],
+ * k_edges[b+1]) (nbins + 1 edges in h/Mpc).  out_counts (optional) receives the number of modes
+ * per shell.  The field is not modified (RF_BUF_AUX is the scratch).  Single-GPU contexts. */
+int rf_r2c_power(rf_ctx* ctx, int nbins, const double* k_edges, double* out_pk, long long* out_counts);
 
 /* Chunked exchange (slab decomposition): the packed z columns (nz/2) are cut into `nchunks`
  * chunks.  Pass 1 of chunk c writes a contiguous send block, the copy engines push its G
@@ -197,12 +222,18 @@ void* rf_device_ptr(rf_ctx* ctx, int which);
 long long rf_buffer_bytes(rf_ctx* ctx, int which);
 /* 1 if the (nx, ny, nz, dtype) grid runs on the tile kernels, 0 if on the generic path */
 int rf_is_fast(rf_ctx* ctx);
-/* 1 if the hot path runs on the persistent TMA-pipelined kernels (k1p/k2p/k3p: float32, axes of
- * 64..1024 points, 2048 for z), 0 if on the rf_fast.cuh tile kernels or the generic path */
+/* 1 if the hot path runs on the persistent TMA-pipelined kernels (float32, axes of 64..4096 points
+ * and -- once rf_set_power has been called -- a sigma table the single-load evaluation covers),
+ * 0 if pass 1 falls back to the rf_fast.cuh tile kernels or the grid is on the generic path */
 int rf_is_pipelined(rf_ctx* ctx);
-/* 0: passes 2 and 3 are separate kernels; 2 / 1: fused in k23q_fused_yz / k23p_fused_yz (whole-field
- * rf_finish_yz only; the chunked exchange always runs them separately) */
+/* 0: passes 2 and 3 are separate kernels; 2: fused in k23q_fused_yz (whole-field rf_finish_yz only;
+ * the chunked exchange runs them separately) */
 int rf_is_fused(rf_ctx* ctx);
+/* "k1;k2;k3": names of the kernels pass 1 / 2 / 3 launch for this context as configured now */
+int rf_kernel_names(rf_ctx* ctx, char* buf, int buflen);
+/* 1: a k-space block is pending (between rf_generate_xpass and rf_finish_yz) or nothing has been
+ * generated; 2: RF_BUF_FIELD holds a real-space field */
+int rf_field_state(rf_ctx* ctx);
 /* number of kernels launched by this context so far */
 long long rf_launch_count(rf_ctx* ctx);
 

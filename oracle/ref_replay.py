@@ -1,8 +1,11 @@
-"""TEST INFRASTRUCTURE ONLY -- loads the UNMODIFIED reference modules from /root/reference.
+"""TEST INFRASTRUCTURE ONLY -- loads the UNMODIFIED reference modules.
 
-Only usable in the build container (the GPU box has no /root/reference).  It exists to
-(1) pin the numpy restatement in oracle/oracle.py against the real reference and
-(2) generate the golden fixtures under tests/golden/ (tests/golden/make_golden.py).
+From /root/reference in the build container; on the GPU box, which has no reference tree, from
+the byte-for-byte staged copy under oracle/_ref/ (git-ignored; recipe and hash manifest:
+oracle/make_ref.py, run by __graft_entry__.build()).  It exists to
+(1) pin the numpy restatement in oracle/oracle.py against the real reference,
+(2) generate the golden fixtures under tests/golden/ (tests/golden/make_golden.py) and
+(3) be the timed CPU arm of bench.py (--impl reference, cpu_baseline.kind = "reference").
 
 The reference is Python-2 era: transform.py / powertools.py / random.py import each other
 with implicit-relative imports and use numpy names removed in numpy 2.  We load them by file
@@ -19,12 +22,21 @@ import sys
 import numpy as np
 
 REFERENCE_ROOT = os.environ.get("RF_REFERENCE_ROOT", "/root/reference")
+_STAGED = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+if not os.path.exists(os.path.join(REFERENCE_ROOT, "randomfield", "transform.py")) and \
+        os.path.exists(os.path.join(_STAGED, "randomfield", "transform.py")):
+    REFERENCE_ROOT = _STAGED
 _PKG = os.path.join(REFERENCE_ROOT, "randomfield")
 _mods = {}
 
 
 def available() -> bool:
     return os.path.exists(os.path.join(_PKG, "transform.py"))
+
+
+def staged() -> bool:
+    """True when the modules come from the staged copy (oracle/_ref) rather than the reference tree."""
+    return REFERENCE_ROOT == _STAGED
 
 
 def _shim_numpy():

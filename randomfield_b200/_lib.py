@@ -16,6 +16,7 @@ LIB_PATH = os.environ.get("RF_LIB") or os.path.join(_HERE, "librf_b200.so")
 
 RF_F32, RF_F64 = 0, 1
 RF_BUF_FIELD, RF_BUF_RECV, RF_BUF_PARTIALS = 0, 1, 2
+RF_BUF_AUX = RF_BUF_RECV
 RF_ERR_ARG, RF_ERR_CUDA, RF_ERR_STATE = -1, -2, -3
 
 # every symbol include/rf_b200.h declares: (name, restype, argtypes)
@@ -30,12 +31,16 @@ SIGNATURES = {
     "rf_sync": (_c.c_int, [_P]),
     "rf_set_power": (_c.c_int, [_P, _c.c_int, _P, _P, _c.c_double]),
     "rf_set_noise": (_c.c_int, [_P, _P]),
+    "rf_set_noise_rows": (_c.c_int, [_P, _P, _c.c_int, _c.c_int]),
     "rf_generate_xpass": (_c.c_int, [_P, _c.c_uint64, _c.c_int]),
     "rf_finish_yz": (_c.c_int, [_P, _P, _c.c_int]),
     "rf_generate_delta": (_c.c_int, [_P, _c.c_uint64, _c.c_int, _P, _c.c_int]),
     "rf_stats": (_c.c_int, [_P, _c.POINTER(_c.c_double), _c.POINTER(_c.c_double), _c.POINTER(_c.c_longlong)]),
     "rf_density": (_c.c_int, [_P, _c.c_int, _c.c_double, _P, _P]),
     "rf_copy_field": (_c.c_int, [_P, _P]),
+    "rf_copy_rows": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_int, _P, _c.c_int]),
+    "rf_copy_wait": (_c.c_int, [_P]),
+    "rf_finish_yz_streamed": (_c.c_int, [_P, _P, _c.c_int, _P, _c.c_int]),
     "rf_field_elems": (_c.c_longlong, [_P]),
     "rf_kspace_public": (_c.c_int, [_P, _c.c_uint64, _c.c_int, _P, _P]),
     "rf_plan_execute": (_c.c_int, [_c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P, _P]),
@@ -56,6 +61,9 @@ SIGNATURES = {
     "rf_set_peer_recv": (_c.c_int, [_P, _c.c_int, _P]),
     "rf_set_direct": (_c.c_int, [_P, _c.c_int]),
     "rf_lensing": (_c.c_int, [_P, _c.c_int, _P]),
+    "rf_r2c_power": (_c.c_int, [_P, _c.c_int, _P, _P, _P]),
+    "rf_kernel_names": (_c.c_int, [_P, _c.c_char_p, _c.c_int]),
+    "rf_field_state": (_c.c_int, [_P]),
     "rf_chunk_config": (_c.c_int, [_P, _c.c_int]),
     "rf_comm_stream": (_c.c_void_p, [_P]),
     "rf_chunk_begin_step": (_c.c_int, [_P]),
@@ -184,6 +192,15 @@ class Engine:
             raise ValueError("noise has {0} values, expected {1}.".format(noise.size, expect))
         check(lib().rf_set_noise(self._ctx, ptr(noise)))
 
+    def set_noise_rows(self, rows, x0):
+        """Upload x rows [x0, x0 + len(rows)) of the white-noise array (rows: float64, shape
+        (n, ny, nz//2+1, 2) or flat)."""
+        rows = np.ascontiguousarray(rows, dtype=np.float64).reshape(-1)
+        per_row = 2 * self.ny * (self.nz // 2 + 1)
+        if rows.size == 0 or rows.size % per_row:
+            raise ValueError("noise rows have {0} values, expected a multiple of {1}.".format(rows.size, per_row))
+        check(lib().rf_set_noise_rows(self._ctx, ptr(rows), int(x0), int(x0) + rows.size // per_row))
+
     # -- hot path -------------------------------------------------------------------------
     def generate_xpass(self, seed, potential=False):
         check(lib().rf_generate_xpass(self._ctx, int(seed) & 0xFFFFFFFFFFFFFFFF, int(bool(potential))))
@@ -196,6 +213,47 @@ class Engine:
         zs = None if zscale is None else np.ascontiguousarray(zscale, dtype=np.float64)
         check(lib().rf_generate_delta(self._ctx, int(seed) & 0xFFFFFFFFFFFFFFFF, int(bool(potential)),
                                       None if zs is None else ptr(zs), int(bool(want_stats))))
+
+    def finish_yz_streamed(self, out, zscale=None, want_stats=True, nranges=8):
+        """rf_finish_yz with the result streamed into the host array `out` (page-locked for full
+        overlap) range by range; call copy_wait() before reading it."""
+        if out.dtype != self.real_dtype or out.shape != self.field_shape or not out.flags.c_contiguous:
+            raise ValueError("bad output array for finish_yz_streamed")
+        zs = None if zscale is None else np.ascontiguousarray(zscale, dtype=np.float64)
+        check(lib().rf_finish_yz_streamed(self._ctx, None if zs is None else ptr(zs), int(bool(want_stats)),
+                                          ptr(out), int(nranges)))
+
+    def copy_rows(self, out_rows, x0, which=RF_BUF_FIELD, wait=True):
+        """Copy local x rows [x0, x0 + len(out_rows)) of the real field (or of RF_BUF_AUX, the
+        lensing potential) into `out_rows` on the copy stream."""
+        if out_rows.dtype != self.real_dtype or out_rows.shape[1:] != (self.ny, self.nz) or \
+                not out_rows.flags.c_contiguous:
+            raise ValueError("bad output array for copy_rows")
+        check(lib().rf_copy_rows(self._ctx, int(which), int(x0), int(x0) + out_rows.shape[0], ptr(out_rows),
+                                 0 if wait else 1), value_error_ok=False)
+        return out_rows
+
+    def copy_wait(self):
+        check(lib().rf_copy_wait(self._ctx))
+
+    def r2c_power(self, k_edges):
+        """Shell-averaged P(k) of the real-space field (rf_r2c_power): returns (Pk, n_modes)."""
+        edges = np.ascontiguousarray(k_edges, dtype=np.float64)
+        nb = len(edges) - 1
+        pk = np.zeros(nb, dtype=np.float64)
+        cnt = np.zeros(nb, dtype=np.int64)
+        check(lib().rf_r2c_power(self._ctx, nb, ptr(edges), ptr(pk), ptr(cnt)))
+        return pk, cnt
+
+    @property
+    def kernel_names(self):
+        buf = ctypes.create_string_buffer(256)
+        check(lib().rf_kernel_names(self._ctx, buf, 256))
+        return tuple(buf.value.decode().split(";"))
+
+    @property
+    def field_is_real(self):
+        return int(lib().rf_field_state(self._ctx)) == 2
 
     def stats(self):
         s1, s2, n = ctypes.c_double(), ctypes.c_double(), ctypes.c_longlong()
@@ -318,7 +376,7 @@ class Engine:
 
     @property
     def fused_yz(self):
-        """0: separate pass-2 / pass-3 kernels, 2: k23q_fused_yz, 1: k23p_fused_yz."""
+        """0: separate pass-2 / pass-3 kernels, 2: k23q_fused_yz."""
         return int(lib().rf_is_fused(self._ctx))
 
     @property
@@ -342,6 +400,8 @@ class Engine:
     def field_tensor(self):
         """The real field [nx/world, ny, nz] as a torch tensor sharing device memory."""
         import torch
+        if not self.field_is_real:
+            raise RuntimeError("the device buffer does not hold a real-space field")
         n = self.nxl * self.ny * self.nz
         t = self.torch_view(RF_BUF_FIELD, n * self.real_dtype.itemsize)
         tdt = torch.float32 if self.real_dtype == np.float32 else torch.float64

@@ -93,14 +93,6 @@ def build(force: bool = False, verbose: bool = False, jobs: int | None = None) -
         objs.append(obj)
         if want(fused_src, obj):
             todo.append((fused_src, obj, ["-DRF_PIPE_N=%d" % n], verbose))
-    f12_src = os.path.join(CSRC, "rf_fuse12_inst.cu")
-    for n in PIPE_SIZES:
-        if n not in (512, 1024):
-            continue
-        obj = os.path.join(BUILD, "fuse12_%d.o" % n)
-        objs.append(obj)
-        if want(f12_src, obj):
-            todo.append((f12_src, obj, ["-DRF_PIPE_N=%d" % n], verbose))
     if todo:
         nj = jobs or min(len(todo), os.cpu_count() or 4)
         with concurrent.futures.ThreadPoolExecutor(nj) as ex:

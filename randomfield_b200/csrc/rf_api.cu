@@ -41,16 +41,16 @@ struct rf_ctx {
   int nxl = 0, nyl = 0;     // local slab extents
   bool fast = false;
   bool pipe = false;        // TMA-pipelined kernels (f32, env RF_PIPE != 0)
-  bool fuse = false;        // fused y+z kernel k23p (env RF_FUSE=1) / k23q (RF_FUSE=2)
-  bool fuse_q = false;      // ... the three-deep in-place ring variant
+  bool fuse = false;        // passes 2 + 3 in one kernel, k23q_fused_yz (env RF_FUSE: 0 off, 2 wherever it fits)
   bool k1q = true;          // pass 1 with two CTAs per SM (env RF_K1Q=0: one-CTA k1p)
+  bool k1r = true;          // pass 1 with two ping-pong groups in one CTA per SM (env RF_K1R=0: k1q)
   bool k3q = true;          // pass 3 with the three-deep in-place ring (env RF_K3Q=0: k3p)
-  bool fuse12 = false;      // passes 1 + 2 in one kernel when nx == ny in {512, 1024}, single GPU (env RF_FUSE12=1)
-  bool pass2_done = false;  // set by the fused kernel: rf_finish_yz starts at pass 3
+  bool pass2_done = false;  // pass 2 already ran per chunk (rf_chunk_pass2): rf_finish_yz starts at pass 3
+  bool big = true;          // 2048 / 4096-point strided axes on the rf_big.cuh kernels (env RF_BIG=0: rf_fast.cuh)
+  bool lens4 = true;        // register-resident lensing scan where nz allows (env RF_LENS4=0: generic scan)
+  int env_lag = 0;          // env RF_LAG: planes between a plane's y pass and its z pass in k23q (0: automatic)
   int hinge_lo = 0, hinge_hi = -1;   // cells of the sigma table the grid's modes can touch
-  unsigned int* zt_done = nullptr;  // [sched_n] per-z-tile counters of the fused pass 1 + 2 kernel
-  int sched_n = 0;
-  unsigned int* sched = nullptr;   // [1 + nxl] ticket + per-plane counters of k23p
+  unsigned int* sched = nullptr;   // [1 + nxl] ticket + per-plane counters of k23q
   void* peer_recv[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   bool direct = false;      // pass 1 stores straight into the peers' receive buffers
   // chunked exchange (rf_chunk_*): the packed z columns are cut into ck_n chunks; pass 1 of chunk
@@ -96,6 +96,10 @@ struct rf_ctx {
   double* lens_dev = nullptr;   // 5 * nz coefficient tables of rf_lensing
   long long launches = 0;
   bool field_is_real = false;
+  bool aux_is_psi = false;          // RF_BUF_AUX (= the receive buffer) holds the lensing potential
+  cudaStream_t copy_stream = nullptr;   // streamed output (rf_copy_rows / rf_finish_yz_streamed)
+  cudaEvent_t ev_copy = nullptr;
+  std::vector<cudaEvent_t> ev_rng;      // per x range of a streamed finish: pass 3 of the range is done
   bool timing = false;
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
@@ -148,29 +152,22 @@ extern "C" int rf_create(int nx, int ny, int nz, int dtype, int rank, int world,
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&c->num_sms, cudaDevAttrMultiProcessorCount, dev);
-    const char* env = getenv("RF_PIPE");
-    c->pipe = c->fast && dtype == RF_F32 && !(env && env[0] == '0');
-    const char* envf = getenv("RF_FUSE");
-    // Passes 2 and 3 in one kernel, the z pass reading the y-pass output from L2.
-    //   RF_FUSE=2: k23q (in-place tiles, three-deep ring, loader + storer warps, dynamic tickets);
-    //              default where it was measured faster than k2p + k3q: both axes <= 1024 and a
-    //              field of 2^26 cells or more (1024^3: 2.77 ms against 2.97 ms);
-    //   RF_FUSE=1: k23p (two-buffer ring; slower, kept for comparison);  RF_FUSE=0: separate kernels.
+    // run-time switches are read once, here
+    auto env_off = [](const char* name) { const char* e = getenv(name); return e && e[0] == '0'; };
+    c->pipe = c->fast && dtype == RF_F32 && !env_off("RF_PIPE");
+    // Passes 2 and 3 in one kernel, the z pass reading the y-pass output from L2:
+    // default where it was measured faster than k2p + k3q -- both axes <= 1024 and a field of 2^26
+    // cells or more; RF_FUSE=2 (or 1): wherever it fits; RF_FUSE=0: separate kernels.
     const bool fuse_ok = c->pipe && ny <= 1024 && nz <= 2048 && nz >= 128;
     const long long cells_local = (long long)(nx / world) * ny * nz;
-    if (envf) {
-      c->fuse = fuse_ok && (envf[0] == '1' || envf[0] == '2');
-      c->fuse_q = c->fuse && envf[0] == '2';
-    } else {
-      c->fuse = c->fuse_q = fuse_ok && nz <= 1024 && cells_local >= (1LL << 26);
-    }
-    const char* envq = getenv("RF_K1Q");
-    c->k1q = !(envq && envq[0] == '0');
-    // opt-in: measured slower than k1q + k2p on B200
-    const char* env3 = getenv("RF_K3Q");
-    c->k3q = !(env3 && env3[0] == '0');
-    const char* env12 = getenv("RF_FUSE12");
-    c->fuse12 = env12 && env12[0] == '1';
+    if (const char* envf = getenv("RF_FUSE")) c->fuse = fuse_ok && (envf[0] == '1' || envf[0] == '2');
+    else c->fuse = fuse_ok && nz <= 1024 && cells_local >= (1LL << 26);
+    c->k1q = !env_off("RF_K1Q");
+    c->k1r = !env_off("RF_K1R");
+    c->k3q = !env_off("RF_K3Q");
+    c->big = !env_off("RF_BIG");
+    c->lens4 = !env_off("RF_LENS4");
+    if (const char* el = getenv("RF_LAG")) c->env_lag = std::max(0, atoi(el));
   }
   RF_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
   c->stream = c->own_stream;
@@ -204,7 +201,7 @@ extern "C" int rf_destroy(rf_ctx* c) {
   if (!c) return RF_OK;
   cudaStreamSynchronize(c->stream);
   void* ptrs[] = {c->field, c->recv, c->partials, c->stats_dev, c->tw_x, c->tw_y, c->tw_z,
-                  c->tw_zh, c->knots, c->cells, c->hinge, c->plane, c->sched, c->zt_done, c->lens_dev, c->noise, c->zs_dev, c->da_dev, c->db_dev};
+                  c->tw_zh, c->knots, c->cells, c->hinge, c->plane, c->sched, c->lens_dev, c->noise, c->zs_dev, c->da_dev, c->db_dev};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   if (c->send) cudaFree(c->send);
@@ -212,6 +209,9 @@ extern "C" int rf_destroy(rf_ctx* c) {
   for (cudaEvent_t ev : c->seg_b) cudaEventDestroy(ev);
   for (cudaEvent_t ev : c->ev_xc) cudaEventDestroy(ev);
   if (c->comm) cudaStreamDestroy(c->comm);
+  for (cudaEvent_t ev : c->ev_rng) cudaEventDestroy(ev);
+  if (c->ev_copy) cudaEventDestroy(c->ev_copy);
+  if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
   for (cudaEvent_t e : {c->ev_k1, c->ev_x, c->ev_s})
     if (e) cudaEventDestroy(e);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -311,10 +311,60 @@ extern "C" int rf_set_direct(rf_ctx* c, int enabled) {
 }
 
 extern "C" int rf_is_fast(rf_ctx* c) { return c && c->fast ? 1 : 0; }
-extern "C" int rf_is_pipelined(rf_ctx* c) {
-  return c && c->pipe && c->nx <= 4096 && c->ny <= 4096 && c->nz <= 4096 ? 1 : 0;
+// pass 1 runs on the TMA-pipelined generator only when the sigma table allows the single-load
+// hinge evaluation (build_table: hinge_ok) and, for 2048 / 4096-point x axes, when the cell table
+// fits in shared memory; otherwise the rf_fast.cuh kernel generates and the x pass
+static bool k1_is_pipelined(rf_ctx* c) {
+  bool k1_pipe = c->pipe && c->nx <= 4096 && c->hinge_ok;
+  if (k1_pipe && c->nx > 1024) {
+    k1_pipe = c->big && (c->nx == 2048 ? PipeLaunch<2048>::k1p_fits(c->noise ? 0 : c->lut_n)
+                                        : PipeLaunch<4096>::k1p_fits(c->noise ? 0 : c->lut_n));
+  }
+  return k1_pipe;
 }
-extern "C" int rf_is_fused(rf_ctx* c) { return c && c->fuse ? (c->fuse_q ? 2 : 1) : 0; }
+extern "C" int rf_is_pipelined(rf_ctx* c) {
+  if (!c || !c->pipe || c->nx > 4096 || c->ny > 4096 || c->nz > 4096) return 0;
+  return (!c->have_power || k1_is_pipelined(c)) ? 1 : 0;
+}
+extern "C" int rf_field_state(rf_ctx* c) { return !c ? 0 : (c->field_is_real ? 2 : 1); }
+static const char* k1_small_name(rf_ctx* c) {
+  bool q = false, r = false;
+  switch (c->nx) {
+    case 64: q = PipeLaunch<64>::k1q_fits(c->lut_n); r = PipeLaunch<64>::k1r_fits(c->lut_n); break;
+    case 128: q = PipeLaunch<128>::k1q_fits(c->lut_n); r = PipeLaunch<128>::k1r_fits(c->lut_n); break;
+    case 256: q = PipeLaunch<256>::k1q_fits(c->lut_n); r = PipeLaunch<256>::k1r_fits(c->lut_n); break;
+    case 512: q = PipeLaunch<512>::k1q_fits(c->lut_n); r = PipeLaunch<512>::k1r_fits(c->lut_n); break;
+    case 1024: q = PipeLaunch<1024>::k1q_fits(c->lut_n); r = PipeLaunch<1024>::k1r_fits(c->lut_n); break;
+  }
+  if (c->k1r && r) return "k1r_generate_xfft";
+  return (c->k1q && q) ? "k1q_generate_xfft" : "k1p_generate_xfft";
+}
+// "k1;k2;k3" -- the kernels rf_generate_xpass / rf_finish_yz launch for this context as configured
+// now (after rf_set_power); a fused y + z pass reports the same name for k2 and k3
+extern "C" int rf_kernel_names(rf_ctx* c, char* buf, int buflen) {
+  if (!c || !buf || buflen < 8) return fail(RF_ERR_ARG, "rf_kernel_names: bad argument");
+  std::string k1, k2, k3;
+  if (!c->fast) {
+    k1 = "gen_kspace_public_kernel+generic_line_fft_kernel"; k2 = k3 = "generic_line_fft_kernel";
+  } else {
+    const bool f32 = c->dtype == RF_F32;
+    if (f32 && c->have_power && k1_is_pipelined(c))
+      k1 = c->nx > 1024 ? "k1b_generate_xfft" : k1_small_name(c);
+    else k1 = "k1_generate_xfft";
+    if (f32 && c->pipe && (c->ny <= 1024 || (c->ny <= 4096 && c->big)))
+      k2 = c->ny > 1024 ? "k2b_strided_fft" : "k2p_strided_fft";
+    else k2 = "k2_strided_fft";
+    if (f32 && c->pipe && c->nz <= 4096) k3 = (c->k3q && c->nz >= 128) ? "k3q_c2r_lines" : "k3p_c2r_lines";   // (nz = 64: the ring does not fit)
+    else k3 = "k3_c2r_lines";
+    if (c->fuse && k2 == "k2p_strided_fft" && (long long)c->ny * (c->nz / 2) * 8 >= pipe::kTileBytes)
+      k2 = k3 = "k23q_fused_yz";
+  }
+  const std::string all = k1 + ";" + k2 + ";" + k3;
+  if ((int)all.size() + 1 > buflen) return fail(RF_ERR_ARG, "rf_kernel_names: buffer too small");
+  memcpy(buf, all.c_str(), all.size() + 1);
+  return RF_OK;
+}
+extern "C" int rf_is_fused(rf_ctx* c) { return c && c->fuse ? 2 : 0; }
 extern "C" long long rf_launch_count(rf_ctx* c) { return c ? c->launches : 0; }
 extern "C" long long rf_field_elems(rf_ctx* c) {
   return c ? (long long)c->nxl * c->ny * c->nz : 0;
@@ -499,18 +549,41 @@ extern "C" int rf_set_power(rf_ctx* c, int n, const double* k, const double* sig
   return e;
 }
 
+// rows x in [x0, x1) of the white-noise array [nx][ny][nz/2+1][2] (contiguous on host and device):
+// the caller may draw and upload the deviates slab by slab without ever holding 16 B per mode on
+// the host (random.py:25-27 notes that the reference's temporary "should" be chunked)
+extern "C" int rf_set_noise_rows(rf_ctx* c, const double* host_rows, int x0, int x1) {
+  if (!c || !host_rows) return fail(RF_ERR_ARG, "rf_set_noise_rows: null argument");
+  if (c->world > 1) return fail(RF_ERR_ARG, "rf_set_noise: single-GPU only");
+  if (x0 < 0 || x1 > c->nx || x0 >= x1) return fail(RF_ERR_ARG, "rf_set_noise_rows: bad x range");
+  const size_t row = (size_t)2 * c->ny * (c->nz / 2 + 1);
+  if (!c->noise) {
+    RF_CUDA(cudaStreamSynchronize(c->stream));
+    RF_CUDA(cudaMalloc((void**)&c->noise, row * c->nx * sizeof(double)));
+  }
+  // ordered after the work already queued on the stream (a previous step may still read the array);
+  // the source is pageable in general, so the call returns once the rows are staged
+  RF_CUDA(cudaMemcpyAsync(c->noise + row * x0, host_rows, row * (x1 - x0) * sizeof(double), cudaMemcpyHostToDevice,
+                          c->stream));
+  RF_CUDA(cudaStreamSynchronize(c->stream));
+  return RF_OK;
+}
+
 extern "C" int rf_set_noise(rf_ctx* c, const double* host_noise) {
   if (!c) return fail(RF_ERR_ARG, "null ctx");
-  if (c->world > 1 && host_noise) return fail(RF_ERR_ARG, "rf_set_noise: single-GPU only");
-  RF_CUDA(cudaStreamSynchronize(c->stream));
   if (!host_noise) {
+    RF_CUDA(cudaStreamSynchronize(c->stream));
     if (c->noise) cudaFree(c->noise);
     c->noise = nullptr;
     return RF_OK;
   }
-  const size_t n = (size_t)2 * c->nx * c->ny * (c->nz / 2 + 1);
-  if (!c->noise) RF_CUDA(cudaMalloc((void**)&c->noise, n * sizeof(double)));
-  RF_CUDA(cudaMemcpy(c->noise, host_noise, n * sizeof(double), cudaMemcpyHostToDevice));
+  // uploaded in slabs of about 256 MB
+  const size_t row = (size_t)2 * c->ny * (c->nz / 2 + 1);
+  const int step = (int)std::max<size_t>(1, ((size_t)32 << 20) / row);
+  for (int x0 = 0; x0 < c->nx; x0 += step) {
+    int e = rf_set_noise_rows(c, host_noise + row * x0, x0, std::min(c->nx, x0 + step));
+    if (e) return e;
+  }
   return RF_OK;
 }
 
@@ -651,15 +724,9 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
   c->stats_valid = false;
   c->pass2_done = false;
   if constexpr (std::is_same<T, float>::value) {
-    bool k1_pipe = c->pipe && c->nx <= 4096 && c->hinge_ok;
-    if (k1_pipe && c->nx > 1024) {
-      // rf_big.cuh kernels stage the sigma cell table in shared memory; 32-byte-wide tiles
-      // (nx = 4096) need nz/2 % 4 == 0, 64-byte ones nz/2 % 8 == 0 -- true for nz >= 64
-      if (c->nx == 2048) k1_pipe = PipeLaunch<2048>::k1p_fits(c->noise ? 0 : c->lut_n);
-      else k1_pipe = PipeLaunch<4096>::k1p_fits(c->noise ? 0 : c->lut_n);
-      const char* eb = getenv("RF_BIG");
-      if (eb && eb[0] == '0') k1_pipe = false;
-    }
+    // (rf_big.cuh kernels stage the sigma cell table in shared memory; 32-byte-wide tiles
+    // (nx = 4096) need nz/2 % 4 == 0, 64-byte ones nz/2 % 8 == 0 -- true for nz >= 64)
+    const bool k1_pipe = k1_is_pipelined(c);
     if (k1_pipe) {
       pipe::K1PParams q;
       q.geom = g; q.tab = tab; q.tw = (const cpx<float>*)c->tw_x;
@@ -701,12 +768,13 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
             int e2 = make_tensor_map(&mout.m[d], base, 3, dout, sout, bout);
             if (e2) return e2;
           }
-          const bool twocta = c->k1q && PipeLaunch<NN>::k1q_fits(c->lut_n);
-          // a few SMs stay free so that the 1-CTA fence collectives between chunks start at once
-          // instead of waiting for a persistent grid to drain
-          int grid = std::min(q.ntiles, (twocta ? 2 : PipeLaunch<NN>::ctas_per_sm()) * (c->num_sms - c->ck_reserve));
-          e = twocta ? PipeLaunch<NN>::k1q(c->noise != nullptr, potential != 0, mout, q, grid, c->stream)
-                     : PipeLaunch<NN>::k1p(c->noise != nullptr, potential != 0, mout, q, grid, c->stream);
+          const bool pingpong = c->k1r && PipeLaunch<NN>::k1r_fits(c->lut_n);
+          const bool twocta = !pingpong && c->k1q && PipeLaunch<NN>::k1q_fits(c->lut_n);
+          // (ck_reserve: SMs left free for the 1-CTA fence collectives between chunks)
+          int grid = std::min(q.ntiles, (twocta ? 2 : (pingpong ? 1 : PipeLaunch<NN>::ctas_per_sm())) * (c->num_sms - c->ck_reserve));
+          e = pingpong ? PipeLaunch<NN>::k1r(c->noise != nullptr, potential != 0, mout, q, grid, c->stream)
+              : twocta ? PipeLaunch<NN>::k1q(c->noise != nullptr, potential != 0, mout, q, grid, c->stream)
+                       : PipeLaunch<NN>::k1p(c->noise != nullptr, potential != 0, mout, q, grid, c->stream);
         });
         c->launches++;
         RF_CUDA(e);
@@ -734,11 +802,13 @@ static int xpass_impl(rf_ctx* c, uint64_t seed, int potential) {
           int e2 = make_tensor_map(&mout.m[0], c->field, 3, dout, sout, bout);
           if (e2) return e2;
         }
-        const bool twocta = c->k1q && PipeLaunch<NN>::k1q_fits(c->lut_n);
-        int grid = std::min(q.ntiles, (twocta ? 2 : PipeLaunch<NN>::ctas_per_sm()) * c->num_sms);
+        const bool pingpong = c->k1r && PipeLaunch<NN>::k1r_fits(c->lut_n);
+        const bool twocta = !pingpong && c->k1q && PipeLaunch<NN>::k1q_fits(c->lut_n);
+        int grid = std::min(q.ntiles, (twocta ? 2 : (pingpong ? 1 : PipeLaunch<NN>::ctas_per_sm())) * c->num_sms);
         mark(c, 0);
-        e = twocta ? PipeLaunch<NN>::k1q(c->noise != nullptr, potential != 0, mout, q, grid, c->stream)
-                   : PipeLaunch<NN>::k1p(c->noise != nullptr, potential != 0, mout, q, grid, c->stream);
+        e = pingpong ? PipeLaunch<NN>::k1r(c->noise != nullptr, potential != 0, mout, q, grid, c->stream)
+            : twocta ? PipeLaunch<NN>::k1q(c->noise != nullptr, potential != 0, mout, q, grid, c->stream)
+                     : PipeLaunch<NN>::k1p(c->noise != nullptr, potential != 0, mout, q, grid, c->stream);
         mark(c, 1);
       });
       c->launches++;
@@ -800,6 +870,95 @@ static int upload_table(rf_ctx* c, void* dst, const double* src, int n) {
   return RF_OK;
 }
 
+// out = field * zs[z], used by the generic path for the light-cone factor
+template <typename T>
+__global__ void scale_z_kernel(T* field, long long n, int nz, const T* zs) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x)
+    field[i] *= __ldg(zs + (int)(i % nz));
+}
+
+// pass 2 (y) of local x rows [x0, x1) on the pipelined kernels (float32); source = the field buffer
+// (one GPU) or the all-to-all receive buffer [src][nxl][nyl][nz/2]
+static int pipe_pass2_rows(rf_ctx* c, int x0, int x1) {
+  const int nzc = c->nz / 2;
+  pipe::K2PParams q;
+  q.tw = (const cpx<float>*)c->tw_y;
+  q.rows_per_src = c->world > 1 ? c->nyl : c->ny;
+  q.out = (cpx<float>*)c->field; q.out_outer = (long long)c->ny * nzc; q.out_row = nzc;
+  q.z_out_base = 0;
+  const void* in = c->world > 1 ? c->recv : c->field;
+  const long long in_outer = (long long)(c->world > 1 ? c->nyl : c->ny) * nzc;
+  const long long in_src = c->world > 1 ? (long long)c->nxl * c->nyl * nzc : in_outer * c->nxl;
+  CUtensorMap min, mout;
+  int e = 0;
+  RF_DISPATCH_PIPE(c->ny, {
+    const int tz = PipeLaunch<NN>::tile_cols();
+    q.ztiles = nzc / tz;
+    q.tile0 = x0 * q.ztiles;
+    q.ntiles = (x1 - x0) * q.ztiles;
+    q.box_rows = std::min(PipeLaunch<NN>::box_rows(), q.rows_per_src);
+    const int nsrc = c->ny / q.rows_per_src;
+    uint64_t din[4] = {(uint64_t)2 * nzc, (uint64_t)q.rows_per_src, (uint64_t)c->nxl, (uint64_t)nsrc};
+    uint64_t sin[3] = {(uint64_t)nzc * 8, (uint64_t)in_outer * 8, (uint64_t)in_src * 8};
+    uint32_t bin[4] = {(uint32_t)2 * tz, (uint32_t)q.box_rows, 1, 1};
+    int e2 = make_tensor_map(&min, (void*)in, 4, din, sin, bin);
+    if (e2) return e2;
+    uint64_t dout[3] = {(uint64_t)2 * nzc, (uint64_t)c->ny, (uint64_t)c->nxl};
+    uint64_t sout[2] = {(uint64_t)nzc * 8, (uint64_t)c->ny * nzc * 8};
+    uint32_t bout[3] = {(uint32_t)2 * tz, (uint32_t)PipeLaunch<NN>::box_rows(), 1};
+    e2 = make_tensor_map(&mout, c->field, 3, dout, sout, bout);
+    if (e2) return e2;
+    const int grid = std::min(q.ntiles, PipeLaunch<NN>::ctas_per_sm() * c->num_sms);
+    e = PipeLaunch<NN>::k2p(min, mout, q, grid, c->stream);
+  });
+  c->launches++;
+  RF_CUDA(e);
+  return RF_OK;
+}
+
+// pass 3 (z, c2r) of local x rows [x0, x1) on the pipelined kernels; statistics partials (one
+// (sum, sumsq) pair per CTA) are appended at c->part_used when want_stats
+static int pipe_pass3_rows(rf_ctx* c, int x0, int x1, const float* zs, int want_stats) {
+  pipe::K3PParams q;
+  q.buf = (float*)c->field;
+  q.twH = (const cpx<float>*)c->tw_zh;
+  q.twN = (const cpx<float>*)c->tw_z;
+  q.zscale = zs;
+  q.partials = nullptr;
+  int e = 0;
+  RF_DISPATCH_PIPE(c->nz, {
+    const int lpt = PipeLaunch<NN>::k3p_lines_per_tile();
+    const long long l0 = (long long)x0 * c->ny, l1 = (long long)x1 * c->ny;
+    if (l0 % lpt || l1 % lpt) return fail(RF_ERR_ARG, "pass 3: the x range does not hold whole tiles");
+    q.tile0 = (int)(l0 / lpt);
+    q.ntiles = (int)((l1 - l0) / lpt);
+    const int grid = std::min(q.ntiles, c->num_sms);
+    if (want_stats) {
+      if (c->part_used + grid > c->parts_cap) return fail(RF_ERR_STATE, "pass 3: statistics buffer too small");
+      q.partials = c->partials + 2 * c->part_used;
+      c->part_used += grid;
+    }
+    e = c->k3q ? PipeLaunch<NN>::k3q(q, grid, c->stream) : PipeLaunch<NN>::k3p(q, grid, c->stream);
+  });
+  c->launches++;
+  RF_CUDA(e);
+  return RF_OK;
+}
+
+static bool pipe_pass2_ok(rf_ctx* c) {
+  return c->dtype == RF_F32 && c->pipe && (c->ny <= 1024 || (c->ny <= 4096 && c->big));
+}
+static bool pipe_pass3_ok(rf_ctx* c) { return c->dtype == RF_F32 && c->pipe && c->nz <= 4096; }
+
+static int finish_stats(rf_ctx* c) {
+  stats_final_kernel<<<1, 256, 0, c->stream>>>(c->partials, c->nparts, c->stats_dev);
+  c->launches++;
+  RF_CUDA(cudaGetLastError());
+  c->stats_valid = true;
+  return RF_OK;
+}
+
 template <typename T>
 static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
   if (c->field_is_real) return fail(RF_ERR_STATE, "rf_finish_yz: no k-space block pending");
@@ -811,111 +970,110 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
   }
   if (c->fast) {
     const int nzc = c->nz / 2;
-    K2Params<T> p2;
-    p2.tw = (const cpx<T>*)c->tw_y;
-    p2.ncols = nzc;
-    p2.scale = (T)1;
-    p2.out = (cpx<T>*)c->field;
-    p2.out_outer = (long long)c->ny * nzc;
-    p2.out_row = nzc;
-    if (c->world > 1) {
-      p2.in = (const cpx<T>*)c->recv;
-      p2.in_outer = (long long)c->nyl * nzc;
-      p2.in_row = nzc;
-      p2.in_src = (long long)c->nxl * c->nyl * nzc;
-      p2.rows_per_src = c->nyl;
-    } else {
-      p2.in = (const cpx<T>*)c->field;
-      p2.in_outer = (long long)c->ny * nzc;
-      p2.in_row = nzc;
-      p2.in_src = 0;
-      p2.rows_per_src = c->ny;
-    }
     int e = 0;
-    bool done2 = false, fused_done = false;
+    bool done2 = false, done3 = false;
     if (c->pass2_done) {
-      // pass 2 already ran inside the fused pass-1 + pass-2 kernel
+      // pass 2 already ran per chunk (rf_chunk_pass2)
       c->pass2_done = false;
       done2 = true;
       mark(c, 2);
       mark(c, 3);
     }
     if constexpr (std::is_same<T, float>::value) {
-      const char* eb2 = getenv("RF_BIG");
-      if (!done2 && c->pipe && (c->ny <= 1024 || (c->ny <= 4096 && !(eb2 && eb2[0] == '0')))) {
-        pipe::K2PParams q;
+      const int t3_per_plane = (int)((long long)c->ny * nzc * 8 / pipe::kTileBytes);
+      if (!done2 && c->fuse && c->ny <= 1024 && pipe_pass2_ok(c) && t3_per_plane >= 1) {
+        // y and z passes in one persistent kernel (the z pass reads the y-pass output from L2)
+        pipe::K23Params f;
+        pipe::K2PParams& q = f.k2;
         q.tw = (const cpx<float>*)c->tw_y;
-        q.rows_per_src = p2.rows_per_src;
-        q.out = (cpx<float>*)p2.out; q.out_outer = p2.out_outer; q.out_row = p2.out_row;
+        q.rows_per_src = c->world > 1 ? c->nyl : c->ny;
+        q.out = (cpx<float>*)c->field; q.out_outer = (long long)c->ny * nzc; q.out_row = nzc;
         q.z_out_base = 0;
+        const void* in = c->world > 1 ? c->recv : c->field;
+        const long long in_outer = (long long)(c->world > 1 ? c->nyl : c->ny) * nzc;
+        const long long in_src = c->world > 1 ? (long long)c->nxl * c->nyl * nzc : in_outer * c->nxl;
         CUtensorMap min, mout;
-        RF_DISPATCH_PIPE(c->ny, {
+        RF_DISPATCH_PIPE1K(c->ny, {
           const int tz = PipeLaunch<NN>::tile_cols();
           q.ztiles = nzc / tz;
+          q.tile0 = 0;
           q.ntiles = c->nxl * q.ztiles;
           q.box_rows = std::min(PipeLaunch<NN>::box_rows(), q.rows_per_src);
           const int nsrc = c->ny / q.rows_per_src;
           uint64_t din[4] = {(uint64_t)2 * nzc, (uint64_t)q.rows_per_src, (uint64_t)c->nxl, (uint64_t)nsrc};
-          uint64_t sin[3] = {(uint64_t)p2.in_row * 8, (uint64_t)p2.in_outer * 8,
-                             (uint64_t)(nsrc > 1 ? p2.in_src : p2.in_outer * c->nxl) * 8};
+          uint64_t sin[3] = {(uint64_t)nzc * 8, (uint64_t)in_outer * 8, (uint64_t)in_src * 8};
           uint32_t bin[4] = {(uint32_t)2 * tz, (uint32_t)q.box_rows, 1, 1};
-          int e2 = make_tensor_map(&min, (void*)p2.in, 4, din, sin, bin);
+          int e2 = make_tensor_map(&min, (void*)in, 4, din, sin, bin);
           if (e2) return e2;
           uint64_t dout[3] = {(uint64_t)2 * nzc, (uint64_t)c->ny, (uint64_t)c->nxl};
-          uint64_t sout[2] = {(uint64_t)p2.out_row * 8, (uint64_t)p2.out_outer * 8};
+          uint64_t sout[2] = {(uint64_t)nzc * 8, (uint64_t)c->ny * nzc * 8};
           uint32_t bout[3] = {(uint32_t)2 * tz, (uint32_t)PipeLaunch<NN>::box_rows(), 1};
-          e2 = make_tensor_map(&mout, (void*)p2.out, 3, dout, sout, bout);
+          e2 = make_tensor_map(&mout, c->field, 3, dout, sout, bout);
           if (e2) return e2;
-          q.tile0 = 0;
-          int grid = std::min(q.ntiles, PipeLaunch<NN>::ctas_per_sm() * c->num_sms);
-          const int t3_per_plane = (int)((long long)c->ny * (c->nz / 2) * 8 / pipe::kTileBytes);
-          if (c->fuse && t3_per_plane >= 1) {
-            // y and z passes in one persistent kernel (z pass reads the y-pass output from L2)
-            pipe::K23Params f;
-            f.k2 = q;
-            f.k3.buf = (float*)c->field;
-            f.k3.twH = (const cpx<float>*)c->tw_zh;
-            f.k3.twN = (const cpx<float>*)c->tw_z;
-            f.k3.zscale = zs;
-            f.k3.partials = nullptr;
-            f.k3.ntiles = 0; f.k3.tile0 = 0;
-            f.nplanes = c->nxl;
-            f.t2 = q.ztiles;
-            f.t3 = t3_per_plane;
-            // measured best with about 5.2 rounds of tickets between a plane's y pass and its z pass
-            // (lag 6 at 1024^3, 24 at 512^3: ~25 MB of y-pass output waiting in L2)
-            f.lag = std::min(c->nxl, std::max(1, (21 * c->num_sms / 4) / (f.t2 + f.t3)));
-            if (c->env_lag > 0) f.lag = std::min(c->nxl, c->env_lag);
-            if (!c->sched) RF_CUDA(cudaMalloc((void**)&c->sched, sizeof(unsigned int) * (1 + c->nxl)));
-            RF_CUDA(cudaMemsetAsync(c->sched, 0, sizeof(unsigned int) * (1 + c->nxl), c->stream));
-            f.ticket = c->sched;
-            f.plane_done = c->sched + 1;
-            const int total = c->nxl * (f.t2 + f.t3);
-            grid = std::min(total, c->num_sms);
-            if (want_stats) {
-              int e2 = ensure_partials(c, grid);
-              if (e2) return e2;
-              f.k3.partials = c->partials;
-            }
-            mark(c, 2);
-            if constexpr (NN <= 1024) e = PipeLaunch<NN>::k23q(c->nz, min, mout, f, grid, c->stream);
-            mark(c, 3);
-            mark(c, 4);
-            mark(c, 5);
-            fused_done = true;
-          } else {
-            mark(c, 2);
-            e = PipeLaunch<NN>::k2p(min, mout, q, grid, c->stream);
-            mark(c, 3);
+          f.k3.buf = (float*)c->field;
+          f.k3.twH = (const cpx<float>*)c->tw_zh;
+          f.k3.twN = (const cpx<float>*)c->tw_z;
+          f.k3.zscale = zs;
+          f.k3.partials = nullptr;
+          f.k3.ntiles = 0; f.k3.tile0 = 0;
+          f.nplanes = c->nxl;
+          f.t2 = q.ztiles;
+          f.t3 = t3_per_plane;
+          // measured best with about 5.2 rounds of tickets between a plane's y pass and its z pass
+          // (lag 6 at 1024^3, 24 at 512^3: ~25 MB of y-pass output waiting in L2)
+          f.lag = std::min(c->nxl, std::max(1, (21 * c->num_sms / 4) / (f.t2 + f.t3)));
+          if (c->env_lag > 0) f.lag = std::min(c->nxl, c->env_lag);
+          if (!c->sched) RF_CUDA(cudaMalloc((void**)&c->sched, sizeof(unsigned int) * (1 + c->nxl)));
+          RF_CUDA(cudaMemsetAsync(c->sched, 0, sizeof(unsigned int) * (1 + c->nxl), c->stream));
+          f.ticket = c->sched;
+          f.plane_done = c->sched + 1;
+          const int total = c->nxl * (f.t2 + f.t3);
+          const int grid = std::min(total, c->num_sms);
+          if (want_stats) {
+            int e2b = ensure_partials(c, grid);
+            if (e2b) return e2b;
+            f.k3.partials = c->partials;
           }
+          mark(c, 2);
+          e = PipeLaunch<NN>::k23q(c->nz, min, mout, f, grid, c->stream);
+          mark(c, 3);
+          mark(c, 4);
+          mark(c, 5);
         });
         c->launches++;
         RF_CUDA(e);
+        done2 = done3 = true;
+      }
+      if (!done2 && pipe_pass2_ok(c)) {
+        mark(c, 2);
+        e = pipe_pass2_rows(c, 0, c->nxl);
+        mark(c, 3);
+        if (e) return e;
         done2 = true;
       }
     }
     if (!done2) {
-    RF_DISPATCH_N(c->ny, {
+      K2Params<T> p2;
+      p2.tw = (const cpx<T>*)c->tw_y;
+      p2.ncols = nzc;
+      p2.scale = (T)1;
+      p2.out = (cpx<T>*)c->field;
+      p2.out_outer = (long long)c->ny * nzc;
+      p2.out_row = nzc;
+      if (c->world > 1) {
+        p2.in = (const cpx<T>*)c->recv;
+        p2.in_outer = (long long)c->nyl * nzc;
+        p2.in_row = nzc;
+        p2.in_src = (long long)c->nxl * c->nyl * nzc;
+        p2.rows_per_src = c->nyl;
+      } else {
+        p2.in = (const cpx<T>*)c->field;
+        p2.in_outer = (long long)c->ny * nzc;
+        p2.in_row = nzc;
+        p2.in_src = 0;
+        p2.rows_per_src = c->ny;
+      }
+      RF_DISPATCH_N(c->ny, {
         int grid = c->nxl * (nzc / FftPlan<T, NN>::TZ);
         mark(c, 2);
         e = Launch<T, NN>::k2(true, p2, grid, c->stream);
@@ -924,36 +1082,23 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
       c->launches++;
       RF_CUDA(e);
     }
-    bool done3 = fused_done;
     if constexpr (std::is_same<T, float>::value) {
-      if (!fused_done && c->pipe && c->nz <= 4096) {
-        pipe::K3PParams q;
-        q.buf = (float*)c->field;
-        q.twH = (const cpx<float>*)c->tw_zh;
-        q.twN = (const cpx<float>*)c->tw_z;
-        q.zscale = zs;
-        q.partials = nullptr;
-        RF_DISPATCH_PIPE(c->nz, {
-          const long long nlines = (long long)c->nxl * c->ny;
-          q.ntiles = (int)(nlines / PipeLaunch<NN>::k3p_lines_per_tile());
-          q.tile0 = 0;
-          int grid = std::min(q.ntiles, c->num_sms);
-          if (want_stats) {
-            int e2 = ensure_partials(c, grid);
-            if (e2) return e2;
-            q.partials = c->partials;
-          }
-          mark(c, 4);
-          e = c->k3q ? PipeLaunch<NN>::k3q(q, grid, c->stream) : PipeLaunch<NN>::k3p(q, grid, c->stream);
-          mark(c, 5);
-        });
-        c->launches++;
-        RF_CUDA(e);
+      if (!done3 && pipe_pass3_ok(c)) {
+        if (want_stats) {
+          int e2 = ensure_partials(c, c->num_sms);
+          if (e2) return e2;
+        }
+        c->part_used = 0;
+        mark(c, 4);
+        e = pipe_pass3_rows(c, 0, c->nxl, zs, want_stats);
+        mark(c, 5);
+        if (e) return e;
+        if (want_stats) c->nparts = c->part_used;
         done3 = true;
       }
     }
     if (!done3) {
-    K3Params<T> p3;
+      K3Params<T> p3;
       p3.buf = (T*)c->field;
       p3.nlines = (long long)c->nxl * c->ny;
       p3.twH = (const cpx<T>*)c->tw_zh;
@@ -989,49 +1134,30 @@ static int finish_impl(rf_ctx* c, const double* zscale, int want_stats) {
     std::swap(c->field, c->recv);
     const long long n = (long long)c->nx * c->ny * c->nz;
     if (want_stats) {
+      // (before the per-z factor, like the tile kernels: generate.py:219 takes the rms of delta)
       int e2 = ensure_partials(c, 1024);
       if (e2) return e2;
       stats_partial_kernel<T><<<1024, 256, 0, c->stream>>>((const T*)c->field, n, c->partials);
       c->launches++;
     }
+    if (zs) {
+      const int grid = (int)std::min<long long>((n + 255) / 256, 148LL * 16);
+      scale_z_kernel<T><<<grid, 256, 0, c->stream>>>((T*)c->field, n, c->nz, zs);
+      c->launches++;
+      RF_CUDA(cudaGetLastError());
+    }
   }
   if (want_stats) {
-    stats_final_kernel<<<1, 256, 0, c->stream>>>(c->partials, c->nparts, c->stats_dev);
-    c->launches++;
-    RF_CUDA(cudaGetLastError());
-    c->stats_valid = true;
+    int e = finish_stats(c);
+    if (e) return e;
   }
   c->field_is_real = true;
-  return RF_OK;
-}
-
-// out = field * zs[z], used by the generic path for the light-cone factor
-template <typename T>
-__global__ void scale_z_kernel(T* field, long long n, int nz, const T* zs) {
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
-       i += (long long)gridDim.x * blockDim.x)
-    field[i] *= __ldg(zs + (int)(i % nz));
-}
-
-template <typename T>
-static int finish_generic_with_scale(rf_ctx* c, const double* zscale, int want_stats) {
-  int e = finish_impl<T>(c, nullptr, want_stats);
-  if (e) return e;
-  e = upload_table<T>(c, c->zs_dev, zscale, c->nz);
-  if (e) return e;
-  const long long n = (long long)c->nx * c->ny * c->nz;
-  int grid = (int)std::min<long long>((n + 255) / 256, 148LL * 16);
-  scale_z_kernel<T><<<grid, 256, 0, c->stream>>>((T*)c->field, n, c->nz, (const T*)c->zs_dev);
-  c->launches++;
-  RF_CUDA(cudaGetLastError());
+  c->aux_is_psi = false;
   return RF_OK;
 }
 
 extern "C" int rf_finish_yz(rf_ctx* c, const double* zscale, int want_stats) {
   if (!c) return fail(RF_ERR_ARG, "null ctx");
-  if (!c->fast && zscale)
-    return c->dtype == RF_F32 ? finish_generic_with_scale<float>(c, zscale, want_stats)
-                              : finish_generic_with_scale<double>(c, zscale, want_stats);
   return c->dtype == RF_F32 ? finish_impl<float>(c, zscale, want_stats)
                             : finish_impl<double>(c, zscale, want_stats);
 }
@@ -1252,7 +1378,7 @@ extern "C" int rf_chunk_pass2_x(rf_ctx* c, int chunk, int x0, int x1, int wait_i
 extern "C" int rf_chunk_pass3_x(rf_ctx* c, int x0, int x1, const double* zscale, int want_stats, int last) {
   if (!c || c->ck_n <= 0) return fail(RF_ERR_STATE, "rf_chunk_pass3_x: chunked path not configured");
   if (x0 < 0 || x1 > c->nxl || x0 > x1) return fail(RF_ERR_ARG, "rf_chunk_pass3_x: bad range");
-  if (!c->pipe || c->nz > 4096) return fail(RF_ERR_STATE, "rf_chunk_pass3_x: pipelined pass 3 not available");
+  if (!pipe_pass3_ok(c)) return fail(RF_ERR_STATE, "rf_chunk_pass3_x: pipelined pass 3 not available");
   const float* zs = nullptr;
   if (zscale) {
     if (!c->zs_loaded) {
@@ -1268,43 +1394,125 @@ extern "C" int rf_chunk_pass3_x(rf_ctx* c, int x0, int x1, const double* zscale,
     if (e) return e;
   }
   if (x1 > x0) {
-    pipe::K3PParams q;
-    q.buf = (float*)c->field;
-    q.twH = (const cpx<float>*)c->tw_zh;
-    q.twN = (const cpx<float>*)c->tw_z;
-    q.zscale = zs;
-    q.partials = nullptr;
-    int e = 0;
-    RF_DISPATCH_PIPE(c->nz, {
-      const int lpt = PipeLaunch<NN>::k3p_lines_per_tile();
-      const long long l0 = (long long)x0 * c->ny, l1 = (long long)x1 * c->ny;
-      if (l0 % lpt || l1 % lpt) return fail(RF_ERR_ARG, "rf_chunk_pass3_x: range does not hold whole tiles");
-      q.tile0 = (int)(l0 / lpt);
-      q.ntiles = (int)((l1 - l0) / lpt);
-      const int grid = std::min(q.ntiles, c->num_sms);
-      if (want_stats) {
-        if (c->part_used + grid > c->parts_cap) return fail(RF_ERR_STATE, "rf_chunk_pass3_x: too many ranges");
-        q.partials = c->partials + 2 * c->part_used;
-        c->part_used += grid;
-      }
-      const int sg = seg_begin(c, 2);
-      e = c->k3q ? PipeLaunch<NN>::k3q(q, grid, c->stream) : PipeLaunch<NN>::k3p(q, grid, c->stream);
-      seg_end(c, sg);
-    });
-    c->launches++;
-    RF_CUDA(e);
+    const int sg = seg_begin(c, 2);
+    int e = pipe_pass3_rows(c, x0, x1, zs, want_stats);
+    seg_end(c, sg);
+    if (e) return e;
   }
   if (last) {
     if (want_stats) {
       c->nparts = c->part_used;
-      stats_final_kernel<<<1, 256, 0, c->stream>>>(c->partials, c->nparts, c->stats_dev);
-      c->launches++;
-      RF_CUDA(cudaGetLastError());
-      c->stats_valid = true;
+      int e = finish_stats(c);
+      if (e) return e;
     }
     c->pass2_done = false;
     c->field_is_real = true;
+    c->aux_is_psi = false;
   }
+  return RF_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// streamed output: pass 2 + pass 3 per range of x rows, each range's
+// device -> host copy on the copy stream while the next range is transformed
+// ------------------------------------------------------------------------------------------
+static int ensure_copy_stream(rf_ctx* c) {
+  if (!c->copy_stream) RF_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+  if (!c->ev_copy) RF_CUDA(cudaEventCreateWithFlags(&c->ev_copy, cudaEventDisableTiming));
+  return RF_OK;
+}
+
+extern "C" int rf_copy_rows(rf_ctx* c, int which, int x0, int x1, void* host_dst, int async) {
+  if (!c || !host_dst) return fail(RF_ERR_ARG, "rf_copy_rows: null argument");
+  if (x0 < 0 || x1 > c->nxl || x0 > x1) return fail(RF_ERR_ARG, "rf_copy_rows: bad x range");
+  const char* src = nullptr;
+  if (which == RF_BUF_FIELD) {
+    if (!c->field_is_real) return fail(RF_ERR_STATE, "rf_copy_rows: no real-space field");
+    src = (const char*)c->field;
+  } else if (which == RF_BUF_AUX) {
+    if (!c->aux_is_psi) return fail(RF_ERR_STATE, "rf_copy_rows: no lensing potential in the auxiliary buffer");
+    src = (const char*)c->recv;
+  } else {
+    return fail(RF_ERR_ARG, "rf_copy_rows: which must be RF_BUF_FIELD or RF_BUF_AUX");
+  }
+  int e = ensure_copy_stream(c);
+  if (e) return e;
+  const size_t row = (size_t)c->ny * c->nz * c->esize;
+  // after everything queued on the compute stream so far
+  RF_CUDA(cudaEventRecord(c->ev_copy, c->stream));
+  RF_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_copy, 0));
+  if (x1 > x0)
+    RF_CUDA(cudaMemcpyAsync(host_dst, src + (size_t)x0 * row, (size_t)(x1 - x0) * row, cudaMemcpyDeviceToHost,
+                            c->copy_stream));
+  if (!async) RF_CUDA(cudaStreamSynchronize(c->copy_stream));
+  return RF_OK;
+}
+
+extern "C" int rf_copy_wait(rf_ctx* c) {
+  if (!c) return fail(RF_ERR_ARG, "null ctx");
+  if (c->copy_stream) RF_CUDA(cudaStreamSynchronize(c->copy_stream));
+  return RF_OK;
+}
+
+extern "C" int rf_finish_yz_streamed(rf_ctx* c, const double* zscale, int want_stats, void* host_dst,
+                                     int nranges) {
+  if (!c || !host_dst) return fail(RF_ERR_ARG, "rf_finish_yz_streamed: null argument");
+  if (c->field_is_real) return fail(RF_ERR_STATE, "rf_finish_yz_streamed: no k-space block pending");
+  int e = ensure_copy_stream(c);
+  if (e) return e;
+  const bool ranged = c->fast && !c->pass2_done && pipe_pass2_ok(c) && pipe_pass3_ok(c) && nranges > 1;
+  int align = 1;
+  if (ranged) {
+    // ranges hold whole pass-3 tiles
+    int lpt = 1;
+    RF_DISPATCH_PIPE(c->nz, { lpt = PipeLaunch<NN>::k3p_lines_per_tile(); });
+    int g = lpt, y = c->ny;
+    while (y) { int t = g % y; g = y; y = t; }
+    align = lpt / g;
+  }
+  const int units = (ranged && c->nxl % align == 0) ? c->nxl / align : 0;
+  const size_t row = (size_t)c->ny * c->nz * c->esize;
+  if (units < 2) {
+    // one range: the whole-field kernels (fused y + z where selected), then one copy
+    e = rf_finish_yz(c, zscale, want_stats);
+    if (e) return e;
+    return rf_copy_rows(c, RF_BUF_FIELD, 0, c->nxl, host_dst, 1);
+  }
+  nranges = std::min(nranges, units);
+  const float* zs = nullptr;
+  if (zscale) {
+    e = upload_table<float>(c, c->zs_dev, zscale, c->nz);
+    if (e) return e;
+    zs = (const float*)c->zs_dev;
+  }
+  if (want_stats) {
+    e = ensure_partials(c, (long long)c->num_sms * nranges);
+    if (e) return e;
+  }
+  c->part_used = 0;
+  while ((int)c->ev_rng.size() < nranges) {
+    cudaEvent_t ev = nullptr;
+    RF_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    c->ev_rng.push_back(ev);
+  }
+  mark(c, 2);
+  for (int r = 0; r < nranges; ++r) {
+    const int x0 = align * (int)((long long)units * r / nranges), x1 = align * (int)((long long)units * (r + 1) / nranges);
+    if (x1 <= x0) continue;
+    if ((e = pipe_pass2_rows(c, x0, x1))) return e;
+    if ((e = pipe_pass3_rows(c, x0, x1, zs, want_stats))) return e;
+    RF_CUDA(cudaEventRecord(c->ev_rng[r], c->stream));
+    RF_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_rng[r], 0));
+    RF_CUDA(cudaMemcpyAsync((char*)host_dst + (size_t)x0 * row, (const char*)c->field + (size_t)x0 * row,
+                            (size_t)(x1 - x0) * row, cudaMemcpyDeviceToHost, c->copy_stream));
+  }
+  mark(c, 3); mark(c, 4); mark(c, 5);
+  if (want_stats) {
+    c->nparts = c->part_used;
+    if ((e = finish_stats(c))) return e;
+  }
+  c->field_is_real = true;
+  c->aux_is_psi = false;
   return RF_OK;
 }
 
@@ -1386,17 +1594,18 @@ static int lensing_impl(rf_ctx* c, int i_min, const double* tables5) {
   LensTables tb;
   tb.cotk = c->lens_dev; tb.pa = c->lens_dev + nz; tb.pb = c->lens_dev + 2 * nz;
   tb.pd = c->lens_dev + 3 * nz; tb.pt = c->lens_dev + 4 * nz;
+  if (!c->recv) RF_CUDA(cudaMalloc(&c->recv, c->buf_bytes));
+  T* const psi = (T*)c->recv;   // generate.py:398-399: psi is a separate array, dPhi stays intact
   const long long nlines4 = (long long)c->nxl * c->ny;
-  const char* el4 = getenv("RF_LENS4");
-  const bool lens4 = !(el4 && el4[0] == '0');
+  const bool lens4 = c->lens4;
   constexpr int S8 = LensS<T>::value;
   auto go = [&](auto kern, int S, int tpb) {
     const int per_sm = std::max(1, (sizeof(T) == 4 && S == 4 ? 768 : 512) / tpb);
     const int lpc = tpb / (nz / S);
     const int grid = (int)std::min<long long>((nlines4 + lpc - 1) / lpc, (long long)c->num_sms * per_sm);
-    kern<<<grid, tpb, 0, c->stream>>>((T*)c->field, nlines4, nz, i_min, tb);
+    kern<<<grid, tpb, 0, c->stream>>>((const T*)c->field, psi, nlines4, nz, i_min, tb);
     c->launches++;
-    c->stats_valid = false;
+    c->aux_is_psi = true;
     return cudaGetLastError();
   };
   // fixed sample ownership: coefficients in registers, 16-byte vectors per thread and line
@@ -1425,9 +1634,9 @@ static int lensing_impl(rf_ctx* c, int i_min, const double* tables5) {
   const long long nlines = (long long)c->nxl * c->ny;
   const int per_sm = std::max(1, (int)((size_t)228 * 1024 / (smem + 1024)));
   const int grid = (int)std::min<long long>((nlines + warps - 1) / warps, (long long)c->num_sms * per_sm);
-  lensing_scan_kernel<T><<<grid, 32 * warps, smem, c->stream>>>((T*)c->field, nlines, nz, i_min, tb);
+  lensing_scan_kernel<T><<<grid, 32 * warps, smem, c->stream>>>((const T*)c->field, psi, nlines, nz, i_min, tb);
   c->launches++;
-  c->stats_valid = false;
+  c->aux_is_psi = true;
   RF_CUDA(cudaGetLastError());
   return RF_OK;
 }
@@ -1457,21 +1666,27 @@ static int kspace_impl(rf_ctx* c, uint64_t seed, int potential, void* host, int3
   SigmaTable<T> tab = make_tab<T>(c);
   const int nzh = c->nz / 2 + 1;
   const long long total = (long long)c->nx * c->nyl * nzh;
+  // generated into scratch memory: in the reference, looking at plan_c2r.data_in / generator.potential
+  // has no side effect on the field (generate.py:84,200-217)
+  cpx<T>* scratch = nullptr;
   int32_t* dbins = nullptr;
-  if (host_bins) RF_CUDA(cudaMalloc((void**)&dbins, sizeof(int32_t) * total));
+  RF_CUDA(cudaMalloc((void**)&scratch, sizeof(cpx<T>) * total));
+  if (host_bins && cudaMalloc((void**)&dbins, sizeof(int32_t) * total) != cudaSuccess) {
+    cudaFree(scratch);
+    return fail(RF_ERR_CUDA, "rf_kspace_public: out of device memory");
+  }
   const double N3 = (double)c->nx * c->ny * c->nz;
   int grid = (int)std::min<long long>((total + 255) / 256, 148LL * 16);
-  gen_kspace_public_kernel<T><<<grid, 256, 0, c->stream>>>(g, tab, (cpx<T>*)c->field, dbins, (T)N3,
-                                                           c->rank * c->nyl, c->nyl);
+  gen_kspace_public_kernel<T><<<grid, 256, 0, c->stream>>>(g, tab, scratch, dbins, (T)N3, c->rank * c->nyl, c->nyl);
   c->launches++;
-  c->field_is_real = false;
-  c->stats_valid = false;
-  RF_CUDA(cudaGetLastError());
-  RF_CUDA(cudaMemcpyAsync(host, c->field, sizeof(cpx<T>) * total, cudaMemcpyDeviceToHost, c->stream));
-  if (host_bins)
-    RF_CUDA(cudaMemcpyAsync(host_bins, dbins, sizeof(int32_t) * total, cudaMemcpyDeviceToHost, c->stream));
-  RF_CUDA(cudaStreamSynchronize(c->stream));
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpyAsync(host, scratch, sizeof(cpx<T>) * total, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess && host_bins)
+    e = cudaMemcpyAsync(host_bins, dbins, sizeof(int32_t) * total, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  cudaFree(scratch);
   if (dbins) cudaFree(dbins);
+  RF_CUDA(e);
   return RF_OK;
 }
 
@@ -1480,6 +1695,113 @@ extern "C" int rf_kspace_public(rf_ctx* c, uint64_t seed, int potential, void* h
   if (!c->have_power) return fail(RF_ERR_STATE, "rf_kspace_public: call rf_set_power first");
   return c->dtype == RF_F32 ? kspace_impl<float>(c, seed, potential, host_cplx, host_bins)
                             : kspace_impl<double>(c, seed, potential, host_cplx, host_bins);
+}
+
+// ------------------------------------------------------------------------------------------
+// P(k) estimator: forward r2c of the real field (the reference's unused
+// plan_r2c seam, generate.py:79-80, transform.py:278-301) + shell binning on the device
+// ------------------------------------------------------------------------------------------
+// |F(k)|^2 of every mode of the half-complex array, binned by |k| into nbins shells.  Modes of the
+// interior planes 0 < iz < nz/2 stand for themselves and their Hermitian partner (weight 2), the
+// planes iz in {0, nz/2} hold both partners (weight 1): sums and counts are over the full k-space.
+template <typename T>
+__global__ void pk_bin_kernel(const cpx<T>* f, int nx, int ny, int nz, double k0x, double k0y, double k0z,
+                              int nbins, const double* __restrict__ edges, double* __restrict__ sums,
+                              unsigned long long* __restrict__ counts) {
+  extern __shared__ __align__(16) unsigned char pk_smem[];
+  double* ss = reinterpret_cast<double*>(pk_smem);
+  unsigned long long* sc = reinterpret_cast<unsigned long long*>(ss + nbins);
+  for (int b = threadIdx.x; b < nbins; b += blockDim.x) { ss[b] = 0.0; sc[b] = 0ull; }
+  __syncthreads();
+  const int nzh = nz / 2 + 1;
+  const long long total = (long long)nx * ny * nzh;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int iz = (int)(i % nzh);
+    const long long r = i / nzh;
+    const int iy = (int)(r % ny), ix = (int)(r / ny);
+    const double jx = ix <= nx / 2 ? ix : ix - nx, jy = iy <= ny / 2 ? iy : iy - ny, jz = iz;
+    const double k = sqrt(jx * jx * k0x * k0x + jy * jy * k0y * k0y + jz * jz * k0z * k0z);
+    if (!(k >= edges[0]) || k >= edges[nbins]) continue;
+    int lo = 0, hi = nbins;   // edges[lo] <= k < edges[hi]
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (edges[mid] <= k) lo = mid; else hi = mid;
+    }
+    const cpx<T> v = f[i];
+    const double p = (double)v.x * (double)v.x + (double)v.y * (double)v.y;
+    const int w = (iz == 0 || iz == nz / 2) ? 1 : 2;
+    atomicAdd(&ss[lo], w * p);
+    atomicAdd(&sc[lo], (unsigned long long)w);
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < nbins; b += blockDim.x) {
+    if (sc[b]) {
+      atomicAdd(&sums[b], ss[b]);
+      atomicAdd(&counts[b], sc[b]);
+    }
+  }
+}
+
+template <typename T>
+static int r2c_power_impl(rf_ctx* c, int nbins, const double* edges, double* out_pk, long long* out_counts) {
+  const int nx = c->nx, ny = c->ny, nz = c->nz, nzh = nz / 2 + 1;
+  // forward transform out of place: field (real, pitch nz) -> auxiliary buffer (complex, pitch nz/2+1);
+  // the real field stays as it is
+  if (!c->recv) RF_CUDA(cudaMalloc(&c->recv, c->buf_bytes));
+  c->aux_is_psi = false;
+  const long long plane = (long long)ny * nzh;
+  int e = run_generic_axis<T>(c, c->field, c->recv, 2, 0, nz, (long long)nx * ny, 1, nz, 0, nzh, 0, 1, 1, (T)1, c->stream);
+  if (e) return e;
+  e = run_generic_axis<T>(c, c->recv, c->recv, 0, 0, ny, nx, nzh, plane, 1, plane, 1, nzh, nzh, (T)1, c->stream);
+  if (e) return e;
+  e = run_generic_axis<T>(c, c->recv, c->recv, 0, 0, nx, ny, nzh, nzh, 1, nzh, 1, plane, plane, (T)1, c->stream);
+  if (e) return e;
+  double* dev = nullptr;
+  const size_t bytes = sizeof(double) * (nbins + 1) + sizeof(double) * nbins + sizeof(unsigned long long) * nbins;
+  RF_CUDA(cudaMalloc((void**)&dev, bytes));
+  double* d_edges = dev;
+  double* d_sums = dev + nbins + 1;
+  unsigned long long* d_counts = reinterpret_cast<unsigned long long*>(d_sums + nbins);
+  cudaError_t ce = cudaMemcpyAsync(d_edges, edges, sizeof(double) * (nbins + 1), cudaMemcpyHostToDevice, c->stream);
+  if (ce == cudaSuccess) ce = cudaMemsetAsync(d_sums, 0, bytes - sizeof(double) * (nbins + 1), c->stream);
+  const double two_pi = 6.283185307179586476925286766559;
+  const long long total = (long long)nx * ny * nzh;
+  const int grid = (int)std::min<long long>((total + 255) / 256, (long long)c->num_sms * 8);
+  if (ce == cudaSuccess) {
+    pk_bin_kernel<T><<<grid, 256, nbins * 16, c->stream>>>((const cpx<T>*)c->recv, nx, ny, nz, two_pi / (nx * c->spacing),
+                                                          two_pi / (ny * c->spacing), two_pi / (nz * c->spacing), nbins,
+                                                          d_edges, d_sums, d_counts);
+    c->launches++;
+    ce = cudaGetLastError();
+  }
+  std::vector<double> sums(nbins);
+  std::vector<unsigned long long> counts(nbins);
+  if (ce == cudaSuccess) ce = cudaMemcpyAsync(sums.data(), d_sums, sizeof(double) * nbins, cudaMemcpyDeviceToHost, c->stream);
+  if (ce == cudaSuccess)
+    ce = cudaMemcpyAsync(counts.data(), d_counts, sizeof(unsigned long long) * nbins, cudaMemcpyDeviceToHost, c->stream);
+  if (ce == cudaSuccess) ce = cudaStreamSynchronize(c->stream);
+  cudaFree(dev);
+  RF_CUDA(ce);
+  // P(k) = <|F(k)|^2> V / N3^2 with F the unnormalised forward transform (numpy rfftn convention)
+  const double N3 = (double)nx * ny * nz, V = N3 * c->spacing * c->spacing * c->spacing;
+  for (int b = 0; b < nbins; ++b) {
+    out_pk[b] = counts[b] ? sums[b] / (double)counts[b] * V / (N3 * N3) : 0.0;
+    if (out_counts) out_counts[b] = (long long)counts[b];
+  }
+  return RF_OK;
+}
+
+extern "C" int rf_r2c_power(rf_ctx* c, int nbins, const double* k_edges, double* out_pk, long long* out_counts) {
+  if (!c || !k_edges || !out_pk) return fail(RF_ERR_ARG, "rf_r2c_power: null argument");
+  if (nbins < 1 || nbins > 2048) return fail(RF_ERR_ARG, "rf_r2c_power: need 1 <= nbins <= 2048");
+  for (int b = 0; b < nbins; ++b)
+    if (!(k_edges[b + 1] > k_edges[b])) return fail(RF_ERR_ARG, "rf_r2c_power: bin edges must be strictly increasing");
+  if (c->world > 1) return fail(RF_ERR_STATE, "rf_r2c_power: single-GPU contexts only");
+  if (!c->field_is_real) return fail(RF_ERR_STATE, "rf_r2c_power: no real-space field");
+  if (!(c->spacing > 0)) return fail(RF_ERR_STATE, "rf_r2c_power: call rf_set_power first (grid spacing)");
+  return c->dtype == RF_F32 ? r2c_power_impl<float>(c, nbins, k_edges, out_pk, out_counts)
+                            : r2c_power_impl<double>(c, nbins, k_edges, out_pk, out_counts);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -46,15 +46,6 @@ struct BPlan<2048> {
   static constexpr int R1 = 16, R2 = 16, R3 = 8, TZ = RF_BIG2048_TZ, NT = RF_BIG2048_NT,
                        CTAS = 8 / RF_BIG2048_TZ;
 };
-// plans of the pass-2 warp group of the fused kernel (rf_fuse12.cuh): 256 threads, 64 KB tiles
-template <>
-struct BPlan<1024> {
-  static constexpr int R1 = 16, R2 = 8, R3 = 8, TZ = 8, NT = 256, CTAS = 1;
-};
-template <>
-struct BPlan<512> {
-  static constexpr int R1 = 8, R2 = 8, R3 = 8, TZ = 16, NT = 256, CTAS = 1;
-};
 template <>
 struct BPlan<4096> {
   static constexpr int R1 = 16, R2 = 16, R3 = 16, TZ = 4, NT = 512, CTAS = 1;

@@ -1,4 +1,4 @@
-// rf_fused_inst.cu -- instantiations of the fused y+z kernel k23p for one NY (all NZ):
+// rf_fused_inst.cu -- instantiations of the fused y+z kernel k23q for one NY (all NZ):
 //   -DRF_PIPE_N=<64..1024>
 #include "rf_launch.h"
 
@@ -11,30 +11,6 @@ namespace rf {
 constexpr int NY = RF_PIPE_N;
 
 template <int NZ>
-static int launch23(const CUtensorMap& in, const CUtensorMap& out, const pipe::K23Params& p, int grid,
-                    cudaStream_t s) {
-  constexpr int smem = pipe::k23p_smem_bytes<NY, NZ>();
-  int e = (int)cudaFuncSetAttribute(pipe::k23p_fused_yz<NY, NZ>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  if (e) return e;
-  pipe::k23p_fused_yz<NY, NZ><<<grid, pipe::kThreads, smem, s>>>(in, out, p);
-  return (int)cudaGetLastError();
-}
-
-template <>
-int PipeLaunch<NY>::k23p(int nz, const CUtensorMap& in, const CUtensorMap& out, const pipe::K23Params& p,
-                         int grid, cudaStream_t s) {
-  switch (nz) {
-    case 64: return launch23<64>(in, out, p, grid, s);
-    case 128: return launch23<128>(in, out, p, grid, s);
-    case 256: return launch23<256>(in, out, p, grid, s);
-    case 512: return launch23<512>(in, out, p, grid, s);
-    case 1024: return launch23<1024>(in, out, p, grid, s);
-    case 2048: return launch23<2048>(in, out, p, grid, s);
-  }
-  return (int)cudaErrorInvalidValue;
-}
-
-template <int NZ>
 static int launch23q(const CUtensorMap& in, const CUtensorMap& out, const pipe::K23Params& p, int grid,
                      cudaStream_t s) {
   constexpr int smem = pipe::k23q_smem_bytes<NY, NZ>();
@@ -44,7 +20,7 @@ static int launch23q(const CUtensorMap& in, const CUtensorMap& out, const pipe::
     pipe::k23q_fused_yz<NY, NZ><<<grid, pipe::kThreadsQ, smem, s>>>(in, out, p);
     return (int)cudaGetLastError();
   } else {
-    return launch23<NZ>(in, out, p, grid, s);   // the ring does not fit: two-buffer kernel
+    return (int)cudaErrorInvalidConfiguration;   // the ring does not fit (nz = 64): rf_create never selects it
   }
 }
 

@@ -1,8 +1,8 @@
 // rf_k23q.cuh -- the y pass and the z (c2r) pass in ONE persistent kernel, three-deep tile ring.
 //
-// Same idea and same tile order as k23p_fused_yz (rf_pipe.cuh): the z pass of an x-plane runs a
-// few planes after its y pass and reads the y-pass output from the write-back L2, so DRAM sees
-// 8 B/cell for both passes instead of 16.  k23p lost to the separate kernels because its ring
+// Tile order of K23Params (rf_pipe.cuh): the z pass of an x-plane runs a few planes after its y
+// pass and reads the y-pass output from the write-back L2, so DRAM sees 8 B/cell for both passes
+// instead of 16.  A first version (round 1, removed) lost to the separate kernels because its ring
 // was two dense buffers plus a shared work buffer: store read-out, dependency probe and the next
 // load were serial on one buffer while the other was being transformed.  Here both tile bodies
 // run IN PLACE in their own buffer (k2q_tile_body below, k3q_tile_body of rf_k3q.cuh: read all,
@@ -98,7 +98,7 @@ __device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
 
 // Two producer warps: the LOADER (decode the next ticket, probe the plane counter, issue the TMA
 // load) and the STORER (TMA store, wait for its read-out, hand the buffer back, signal finished
-// planes).  In k23p one thread did all of that in sequence, and that chain of long-latency
+// planes).  In the first version one thread did all of that in sequence, and that chain of long-latency
 // steps (read-out wait, acquire probe, release signal: about 3 us) was longer than a tile's
 // butterflies.
 constexpr int kThreadsQ = kConsumers + 64;
@@ -260,15 +260,11 @@ k23q_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant_
       load_step_twiddles_smem<P2::R1>(twr, tw2s, tid / P2::TZ);
       k2q_tile_body<NY>(B, tid, twr);
     } else {
-      cpx<float> twr[P3::R1];
+      cpx<float> twr[P3::R1], twr2[P3::R1];
       cpx<float> twu[K3Consts<NZ>::kPairsPerThread];
-      sfor<0, K3Consts<NZ>::kPairsPerThread>([&](auto qi) {
-        constexpr int q = decltype(qi)::value;
-        twu[q] = ld_cpx(twNs + (tid + q * kConsumers) % (P3::H / 2));
-      });
-      load_step_twiddles_smem<P3::R1>(twr, twHs, tid % P3::M);
+      k3q_load_twiddles<NZ>(twr, twr2, twu, twHs, twNs, tid, [](const cpx<float>* q) { return ld_cpx(q); });
       cpx<float> a1 = {0.f, 0.f}, a2 = {0.f, 0.f};
-      k3q_tile_body<NZ>(B, tid, twr, twu, zs, a1, a2, p.k3.twH);
+      k3q_tile_body<NZ>(B, tid, twr, twr2, twu, zs, a1, a2, p.k3.twH);
       s1 += (double)a1.x + (double)a1.y;
       s2 += (double)a2.x + (double)a2.y;
     }

@@ -18,10 +18,56 @@ constexpr int k3q_smem_bytes() {
   return 3 * LPlan<NZ>::kWorkBytes + kBarBytes;
 }
 
+// Fused Hermitian unpack (NZ = 256, 512, 1024): the pair (k, H-k) of the unpack lives in the step-A
+// items j and M - j of the same line (k = j + M m  <->  H - k = (M - j) + M (R1 - 1 - m)), so a thread
+// that owns BOTH items unpacks in registers while it loads step A: the separate unpack sweep (one
+// more read and one more write of the tile through shared memory, and its barrier) goes away.
+// Thread -> (p, line), p = tid % (M/2): items (p, M - p) for p >= 1 and the two self-paired items
+// (0, M/2) for p = 0.  The unpack twiddle exp(2 pi i k / NZ) = W_NZ^j * W_(2 R1)^m is one per-thread
+// value times a compile-time 32nd root of unity.
+template <int NZ>
+struct K3Fuse {
+  using P = LPlan<NZ>;
+  static constexpr bool value = P::SPLIT == 1 && (P::R1 == 16 || P::R1 == 8) && P::M >= 4 &&
+                                (P::M * P::TE == 2 * kConsumers) && NZ >= 256;
+  static constexpr int kStep = 32 / (2 * P::R1);   // W_(2 R1)^m = W_32^(kStep m)
+};
+
+// twiddles of this thread for k3q_tile_body: step-A factors of its item(s) and the unpack factor(s).
+// tabH holds exp(2 pi i k / H), tabN exp(2 pi i k / NZ) (global memory or shared-memory copies).
+template <int NZ, class LD>
+__device__ __forceinline__ void k3q_load_twiddles(cpx<float> (&twr)[LPlan<NZ>::R1], cpx<float> (&twr2)[LPlan<NZ>::R1],
+                                                  cpx<float> (&twu)[K3Consts<NZ>::kPairsPerThread],
+                                                  const cpx<float>* tabH, const cpx<float>* tabN, int tid, LD&& ld) {
+  using P = LPlan<NZ>;
+  constexpr int H = P::H, M = P::M, R1 = P::R1;
+  if constexpr (K3Fuse<NZ>::value) {
+    const int pp = tid % (M / 2);
+    const int j0 = pp, j1 = pp == 0 ? M / 2 : M - pp;
+    sfor<0, R1>([&](auto ki) {
+      constexpr int k1 = decltype(ki)::value;
+      twr[k1] = ld(tabH + P::SPLIT * j0 * k1);
+      twr2[k1] = ld(tabH + P::SPLIT * j1 * k1);
+    });
+    twu[0] = ld(tabN + (pp == 0 ? M / 2 : pp));
+  } else {
+    sfor<0, K3Consts<NZ>::kPairsPerThread>([&](auto qi) {
+      constexpr int q = decltype(qi)::value;
+      twu[q] = ld(tabN + (tid + q * kConsumers) % (H / 2));
+    });
+    sfor<0, R1>([&](auto ki) {
+      constexpr int k1 = decltype(ki)::value;
+      twr[k1] = ld(tabH + P::SPLIT * (tid % M) * k1);
+      twr2[k1] = twr[k1];
+    });
+  }
+}
+
 // one tile, in place in `B` (dense [TL][H] at the start of a kWorkBytes buffer)
 template <int NZ>
 __device__ __forceinline__ void k3q_tile_body(cpx<float>* __restrict__ B, int tid,
                                               const cpx<float> (&twr)[LPlan<NZ>::R1],
+                                              const cpx<float> (&twr2)[LPlan<NZ>::R1],
                                               const cpx<float> (&twu)[K3Consts<NZ>::kPairsPerThread],
                                               const float* zs, cpx<float>& a1, cpx<float>& a2, const cpx<float>* twH) {
   using P = LPlan<NZ>;
@@ -31,6 +77,77 @@ __device__ __forceinline__ void k3q_tile_body(cpx<float>* __restrict__ B, int ti
   constexpr int IA = M * P::TE / kConsumers, IB = R1 * P::TE / kConsumers;
   static_assert(IA * kConsumers == M * P::TE && IB * kConsumers == R1 * P::TE, "items per thread");
   static_assert(IA * R1 == 32 && IB * R2 == 32, "32 values per thread and step");
+  if constexpr (K3Fuse<NZ>::value) {
+    // ---- fused: dense -> registers (+ Hermitian unpack) | barrier | registers -> padded ----
+    static_assert(IA == 2, "two items per thread");
+    constexpr int PH = M / 2, KS = K3Fuse<NZ>::kStep;
+    const int pp = tid % PH, l = tid / PH;
+    const int j0 = pp, j1 = pp == 0 ? PH : M - pp;
+    const cpx<float>* Lp = B + l * HE;
+    cpx<float> v0[R1], v1[R1];
+    sfor<0, R1>([&](auto mi) {
+      constexpr int m = decltype(mi)::value;
+      v0[m] = ld_cpx(Lp + j0 + M * m);
+      v1[m] = ld_cpx(Lp + j1 + M * m);
+    });
+    ConsumerSync()();
+    // twu[0] = W_NZ^j0 (p >= 1) / W_NZ^(M/2) (p = 0): the caller loads it for this mapping
+    const cpx<float> wj = twu[0];
+    if (pp != 0) {
+      // k = j0 + M m (item 0)  <->  H - k = j1 + M (R1 - 1 - m) (item 1)
+      sfor<0, R1>([&](auto mi) {
+        constexpr int m = decltype(mi)::value;
+        const cpx<float> a = v0[m], c = v1[R1 - 1 - m];
+        const cpx<float> e = pk_add(a.x, a.y, c.x, -c.y);
+        const cpx<float> d = pk_add(a.x, a.y, -c.x, c.y);
+        const cpx<float> o = mul_tw32<KS * m, true>(cmul(d, wj));
+        v0[m] = pk_add(e.x, e.y, -o.y, o.x);
+        v1[R1 - 1 - m] = pk_add(e.x, -e.y, o.y, o.x);
+      });
+    } else {
+      // item 0 (j = 0): k = M m <-> M (R1 - m); k = 0 and k = H/2 (m = R1/2) are the real ends
+      {
+        cpx<float> z0, zm;
+        c2r_unpack_ends(v0[0], v0[R1 / 2], z0, zm);
+        v0[0] = z0;
+        v0[R1 / 2] = zm;
+      }
+      sfor<1, R1 / 2>([&](auto mi) {
+        constexpr int m = decltype(mi)::value;
+        const cpx<float> a = v0[m], c = v0[R1 - m];
+        const cpx<float> e = pk_add(a.x, a.y, c.x, -c.y);
+        const cpx<float> d = pk_add(a.x, a.y, -c.x, c.y);
+        const cpx<float> o = mul_tw32<KS * m, true>(d);
+        v0[m] = pk_add(e.x, e.y, -o.y, o.x);
+        v0[R1 - m] = pk_add(e.x, -e.y, o.y, o.x);
+      });
+      // item 1 (j = M/2): k = M/2 + M m <-> M/2 + M (R1 - 1 - m)
+      sfor<0, R1 / 2>([&](auto mi) {
+        constexpr int m = decltype(mi)::value;
+        const cpx<float> a = v1[m], c = v1[R1 - 1 - m];
+        const cpx<float> e = pk_add(a.x, a.y, c.x, -c.y);
+        const cpx<float> d = pk_add(a.x, a.y, -c.x, c.y);
+        const cpx<float> o = mul_tw32<KS * m, true>(cmul(d, wj));
+        v1[m] = pk_add(e.x, e.y, -o.y, o.x);
+        v1[R1 - 1 - m] = pk_add(e.x, -e.y, o.y, o.x);
+      });
+    }
+    fft_dif<R1, true>(v0);
+    fft_dif<R1, true>(v1);
+    cpx<float>* wp0 = B + L::idx2(0, j0, l);
+    cpx<float>* wp1 = B + L::idx2(0, j1, l);
+    sfor<0, R1>([&](auto ki) {
+      constexpr int k1 = decltype(ki)::value;
+      cpx<float> x0 = v0[brev<R1>(k1)], x1 = v1[brev<R1>(k1)];
+      if constexpr (k1 > 0) {
+        x0 = cmul(x0, twr[k1]);
+        x1 = cmul(x1, twr2[k1]);
+      }
+      st_cpx(wp0 + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), x0);
+      st_cpx(wp1 + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), x1);
+    });
+    ConsumerSync()();
+  } else {
   // ---- Hermitian unpack, in place (as k3_tile_body) ----
   if constexpr (H / 2 >= kConsumers) {
 #pragma unroll 2
@@ -103,6 +220,7 @@ __device__ __forceinline__ void k3q_tile_body(cpx<float>* __restrict__ B, int ti
     });
   });
   ConsumerSync()();
+  }   // (!K3Fuse)
   // ---- step B: padded -> registers | barrier | registers -> dense (+ statistics, z scale) ----
   cpx<float> u[IB][R2];
   sfor<0, IB>([&](auto qi) {
@@ -194,15 +312,15 @@ __global__ void __launch_bounds__(kThreads, 1) k3q_c2r_lines(const K3PParams p) 
 
   double s1 = 0.0, s2 = 0.0;
   const float* zs = p.zscale;
-  cpx<float> twr[P::R1];
+  cpx<float> twr[P::R1], twr2[P::R1];
   cpx<float> twu[K3Consts<NZ>::kPairsPerThread];
-  k3_load_twiddles<NZ>(twr, twu, p.twH, p.twN, tid);
+  k3q_load_twiddles<NZ>(twr, twr2, twu, p.twH, p.twN, tid, [](const cpx<float>* q) { return ldg_cpx(q); });
   int b = 0, ph = 0;
   for (int t = first; t < p.ntiles; t += step) {
     cpx<float>* const B = buf0 + b * kBufElems;
     mbar_wait(&full[b], ph);
     cpx<float> a1 = {0.f, 0.f}, a2 = {0.f, 0.f};
-    k3q_tile_body<NZ>(B, tid, twr, twu, zs, a1, a2, p.twH);
+    k3q_tile_body<NZ>(B, tid, twr, twr2, twu, zs, a1, a2, p.twH);
     s1 += (double)a1.x + (double)a1.y;
     s2 += (double)a2.x + (double)a2.y;
     fence_proxy_async();

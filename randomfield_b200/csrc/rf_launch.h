@@ -5,7 +5,6 @@
 #include "rf_fast.cuh"
 #include "rf_pipe.cuh"
 #include "rf_big.cuh"
-#include "rf_fuse12.cuh"
 #include "rf_k3q.cuh"
 #include "rf_k23q.cuh"
 
@@ -30,21 +29,17 @@ struct PipeLaunch {
   static int k2p(const CUtensorMap& in, const CUtensorMap& out, const pipe::K2PParams& p, int grid,
                  cudaStream_t s);
   static int k1p(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s);
-  // fused y + z pass (this N = ny); nz in 64..2048
-  static int k23p(int nz, const CUtensorMap& in, const CUtensorMap& out, const pipe::K23Params& p, int grid,
-                  cudaStream_t s);
-  // same with in-place tile bodies and a three-deep ring (rf_k23q.cuh)
+  // fused y + z pass (this N = ny <= 1024; nz in 128..2048): in-place tile bodies, three-deep ring (rf_k23q.cuh)
   static int k23q(int nz, const CUtensorMap& in, const CUtensorMap& out, const pipe::K23Params& p, int grid,
                   cudaStream_t s);
   // two-CTAs-per-SM variant of k1p; hinge_cells = entries of the sigma cell table staged in
   // shared memory.  k1q_fits() says whether that table fits next to the work buffer.
   static int k1q(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s);
   static bool k1q_fits(int hinge_cells);
+  // ping-pong variant: one 512-thread CTA per SM, two groups alternating generate / transform (N <= 1024)
+  static int k1r(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s);
+  static bool k1r_fits(int hinge_cells);
   static bool k1p_fits(int hinge_cells);   // false: the sigma cell table does not fit (rf_big.cuh kernels)
-  // fused pass 1 + pass 2 (rf_fuse12.cuh; nx == ny == N <= 1024, single GPU, Philox path)
-  static int k12(bool potential, const pipe::K1PMaps& maps, const CUtensorMap& in, const CUtensorMap& out,
-                 const fuse12::K12Params& p, int grid, cudaStream_t s);
-  static bool k12_fits(int hinge_cells);
   static int ctas_per_sm();  // resident CTAs per SM of k2p / k1p (grid = this * SM count)
   static int tile_cols();   // TZ
   static int box_rows();    // rows per TMA box of the store map

@@ -843,15 +843,170 @@ k1q_generate_xfft(const __grid_constant__ K1PMaps maps, const K1PParams p) {
 }
 
 // ----------------------------------------------------------------------------------------
-// k23p: the y pass and the z (c2r) pass in ONE persistent kernel, so that the y-pass output of
-// an x-plane is still in L2 when the z pass reads it (the plane's tiles are visited a few
-// planes later, and the 126 MB L2 is write-back): DRAM sees 8 B/cell for both passes instead
-// of 16.  Tiles are handed out by a global ticket in a fixed order
+// k1r: k1q's tile body run by TWO 256-thread groups of one 512-thread CTA that take turns
+// ("ping-pong").  A tile has two phases that want different pipes: GENERATE (Philox = IMAD.WIDE,
+// measured at 1.6 warp instructions per clock and SM on B200; Box-Muller and sigma(k) = MUFU at
+// 16 lanes per clock) and TRANSFORM (radix-32 butterflies on the FP32 pipe, four passes through
+// shared memory).  Two independent CTAs per SM (k1q) start together and, contending
+// symmetrically, stay in lockstep: both generate, then both transform, and every pipe idles half
+// of the time (ncu: no pipe above 35 %, issue slots 56 % busy, yet 2 CTAs per SM are only 11 %
+// faster than one).  Here the two groups hand a token back and forth through named barriers:
+// a group generates only while it holds the token and passes it on before it transforms, so one
+// group's GENERATE always overlaps the other's TRANSFORM.
+//   bar 1 + g : the 256 threads of group g (the __syncthreads of k1q)
+//   bar 3 + g : group g may generate (bar.sync by group g, bar.arrive by the other group)
+// ----------------------------------------------------------------------------------------
+constexpr int kGroupsR = 2;
+constexpr int kThreadsR = kGroupsR * kConsumers;
+
+template <int NX>
+constexpr int k1r_smem_bytes(int hinge_cells) {
+  return kGroupsR * SPlan<NX>::kWorkBytes + NX * 8 + hinge_cells * 16;
+}
+
+__device__ __forceinline__ void named_sync(int id, int count) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+__device__ __forceinline__ void named_arrive(int id, int count) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+
+template <int NX, bool INJ, bool POT>
+__global__ void __launch_bounds__(kThreadsR, 1)
+k1r_generate_xfft(const __grid_constant__ K1PMaps maps, const K1PParams p) {
+  using P = SPlan<NX>;
+  using L = LayoutStridedPad<P::TZ, P::M>;
+  constexpr int R1 = P::R1, R2 = P::R2, M = P::M, TZ = P::TZ;
+  static_assert(M * TZ == kConsumers, "one step-A item per thread");
+  static_assert(R1 % R2 == 0, "step B items per thread");
+  constexpr int IB = R1 / R2;          // step-B items per thread (R1*TZ items / 256 threads)
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int grp = threadIdx.x / kConsumers, tid = threadIdx.x % kConsumers;
+  cpx<float>* const work = reinterpret_cast<cpx<float>*>(smem_raw + grp * P::kWorkBytes);
+  cpx<float>* const tws = reinterpret_cast<cpx<float>*>(smem_raw + kGroupsR * P::kWorkBytes);
+  float4* const hinge_s = reinterpret_cast<float4*>(smem_raw + kGroupsR * P::kWorkBytes + NX * 8);
+  if (threadIdx.x == 0) tma_prefetch_desc(&maps.m[0]);
+  // tws[k1 * M + j] = W_NX^(j * k1): the lanes of a warp (consecutive j) read consecutive words
+  for (int q = threadIdx.x; q < NX; q += kThreadsR) tws[q] = ldg_cpx(p.tw + (q % M) * (q / M));
+  if constexpr (!INJ) {
+    for (int q = threadIdx.x; q < p.tab.lut_n; q += kThreadsR)
+      hinge_s[q] = __ldg(reinterpret_cast<const float4*>(p.tab.hinge) + q);
+  }
+  __syncthreads();
+  const float4* const hinge0 = hinge_s - p.tab.lut_base;   // entry of cell id 0 (never dereferenced)
+  const int shift = p.tab.shift;
+  const int bar_grp = 1 + grp, bar_mine = 3 + grp, bar_other = 3 + (1 - grp);
+  // group 0 holds the token first
+  if (grp == 1) named_arrive(3, kThreadsR);
+
+  const ModeGeom<float>& g = p.geom;
+  const int c = tid % TZ, j = tid / TZ;
+  const int nzh = g.nz / 2 + 1;
+  const float fj = (float)j;
+  const uint64_t dq = (uint64_t)M * g.ny * nzh;   // Philox counter step between m and m+1
+  cpx<float>* const wa = work + L::idx2(0, j, c);
+  // tiles of this CTA: blockIdx.x + k * gridDim.x; group g takes k = g, g + 2, ...
+  const int step = gridDim.x;
+  for (int t = blockIdx.x + grp * step; t < p.ntiles; t += kGroupsR * step) {
+    const int iyl = t / p.ztiles, z0 = (t % p.ztiles) * TZ;
+    const int iy = p.y0 + iyl;
+    const int iz = p.z_base + z0 + c;
+    cpx<float> v[R1];
+    named_sync(bar_mine, kThreadsR);              // ---- GENERATE: this group holds the token ----
+    if (iz == 0) {
+      // packed column (iz=0 plane) + i*(iz=nz/2 plane): precomputed by gen_packed_plane_kernel
+      const cpx<float>* pp = p.plane + (size_t)j * p.ny_local + iyl;
+      sfor<0, R1>([&](auto mi) {
+        constexpr int m = decltype(mi)::value;
+        v[m] = ldg_cpx(pp + (size_t)(M * m) * p.ny_local);
+      });
+    } else if constexpr (INJ) {
+      sfor<0, R1>([&](auto mi) {
+        constexpr int m = decltype(mi)::value;
+        v[m] = raw_mode(g, p.tab, j + M * m, iy, iz);
+      });
+    } else {
+      const float ksq_yz = ksq_canon(0.f, mode_sq<float>(iy, g.ny), mode_sq<float>(iz, g.nz), g.k0x2,
+                                     g.k0y2, g.k0z2);
+      const uint64_t q0 = ((uint64_t)j * g.ny + iy) * nzh + iz;
+      sfor<0, R1 / 2>([&](auto mi) {
+        constexpr int m = decltype(mi)::value;
+        const float f1 = fj + (float)(M * m), f2 = f1 - (float)(NX / 2);
+        const float ks1 = __fmaf_rn(f1 * f1, g.k0x2, ksq_yz);
+        const float ks2 = __fmaf_rn(f2 * f2, g.k0x2, ksq_yz);
+        float s1 = sigma_hinge_smem(hinge0, shift, ks1), s2 = sigma_hinge_smem(hinge0, shift, ks2);
+        if constexpr (POT) {
+          s1 = __fdividef(s1, ks1);   // k^2 > 0 off the iz = 0 plane
+          s2 = __fdividef(s2, ks2);
+        }
+        const uint64_t q = q0 + (uint64_t)m * dq;
+        philox_out o = philox4x32_10((uint32_t)q, (uint32_t)(q >> 32), 0u, 0u, g.key0, g.key1);
+        cpx<float> n1 = box_muller<float>(o.w[0], o.w[1]);
+        cpx<float> n2 = box_muller<float>(o.w[2], o.w[3]);
+        v[m] = pk_mul(n1.x, n1.y, s1, s1);
+        v[m + R1 / 2] = pk_mul(n2.x, n2.y, s2, s2);
+      });
+    }
+    // ---- TRANSFORM: pass the token on if the other group has a tile left ----
+    if (t + step < p.ntiles) named_arrive(bar_other, kThreadsR);
+    fft_dif<R1, true>(v);
+    // the previous tile's TMA store must have finished reading this group's buffer
+    if (tid == 0) bulk_wait_read0();
+    named_sync(bar_grp, kConsumers);
+    sfor<0, R1>([&](auto ki) {
+      constexpr int k1 = decltype(ki)::value;
+      cpx<float> x = v[brev<R1>(k1)];
+      if constexpr (k1 > 0) x = cmul(x, ld_cpx(tws + k1 * M + j));
+      st_cpx(wa + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), x);
+    });
+    named_sync(bar_grp, kConsumers);
+    // step B in place: item w = tid + q*256 -> (k1, column) = (w / TZ, w % TZ)
+    cpx<float> u[IB][R2];
+    sfor<0, IB>([&](auto qi) {
+      constexpr int q = decltype(qi)::value;
+      const int w = tid + q * kConsumers;
+      const cpx<float>* wp = work + L::idx2(w / TZ, 0, w % TZ);
+      sfor<0, R2>([&](auto ji) {
+        constexpr int jj = decltype(ji)::value;
+        u[q][jj] = ld_cpx(wp + (L::idx2(0, jj, 0) - L::idx2(0, 0, 0)));
+      });
+    });
+    named_sync(bar_grp, kConsumers);
+    sfor<0, IB>([&](auto qi) {
+      constexpr int q = decltype(qi)::value;
+      const int w = tid + q * kConsumers;
+      const int k1 = w / TZ, cc = w % TZ;
+      fft_dif<R2, true>(u[q]);
+      sfor<0, R2>([&](auto ki) {
+        constexpr int k2 = decltype(ki)::value;
+        st_cpx(work + (k1 + R1 * k2) * TZ + cc, u[q][brev<R2>(k2)]);
+      });
+    });
+    fence_proxy_async();
+    named_sync(bar_grp, kConsumers);
+    if (tid == 0) {
+      // boxes never straddle two destinations (box rows = min(256, nxl), both powers of two)
+      const int box = p.nxl < P::kBoxRows ? p.nxl : P::kBoxRows;
+      for (int r0 = 0; r0 < NX; r0 += box) {
+        const int d = r0 / p.nxl;
+        tma_store_3d(&maps.m[d], work + r0 * TZ, 2 * z0, iyl, r0 - d * p.nxl);
+      }
+      bulk_commit();
+    }
+  }
+  if (tid == 0) bulk_wait0();
+}
+
+// ----------------------------------------------------------------------------------------
+// Tile schedule of the fused y + z pass (k23q_fused_yz, rf_k23q.cuh): the y pass and the z (c2r)
+// pass in ONE persistent kernel, so that the y-pass output of an x-plane is still in L2 when the
+// z pass reads it (the plane's tiles are visited a few planes later, and the 126 MB L2 is
+// write-back): DRAM sees 8 B/cell for both passes instead of 16.  Tiles are handed out by a
+// global ticket in a fixed order
 //     K2(plane 0) ... K2(plane lag-1), K2(plane lag), K3(plane 0), K2(plane lag+1), K3(plane 1), ...
-// (CTA c owns tickets c, c + grid, c + 2*grid, ...).  A K3 tile waits until the ztiles K2 tiles of
-// its plane have been stored (plane_done counter).  It only depends on smaller tickets and every
-// CTA works through its tickets in increasing order, blocking only when all of its own earlier
-// tiles are stored and signalled, so the smallest unfinished ticket can always proceed.
+// A K3 tile waits until the ztiles K2 tiles of its plane have been stored (plane_done counter).
+// It only depends on smaller tickets and every CTA works through its tickets in increasing
+// order, so the smallest unfinished ticket can always proceed.
 // ----------------------------------------------------------------------------------------
 struct K23Params {
   K2PParams k2;               // ntiles / tile0 unused
@@ -881,226 +1036,6 @@ __device__ __forceinline__ void k23_decode(const K23Params& p, unsigned int tick
   }
   u -= mid;
   type = kTileK3; plane = p.nplanes - p.lag + u / p.t3; idx = u % p.t3;
-}
-
-template <int NY, int NZ>
-constexpr int k23p_smem_bytes() {
-  // dense ring, work buffer, barriers + tile descriptors, twiddle tables (NY + 2*(NZ/2) entries)
-  return 2 * kTileBytes + (SPlan<NY>::kWorkBytes > LPlan<NZ>::kWorkBytes ? SPlan<NY>::kWorkBytes
-                                                                          : LPlan<NZ>::kWorkBytes) + 2 * kBarBytes +
-         (NY + NZ) * 8;
-}
-
-template <int NY, int NZ>
-__global__ void __launch_bounds__(kThreads, 1)
-k23p_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_out,
-              const K23Params p) {
-  using P2 = SPlan<NY>;
-  using P3 = LPlan<NZ>;
-  static_assert(P2::kDenseBytes <= kTileBytes && P3::kDenseBytes <= kTileBytes, "tile size");
-  constexpr int kWork = SPlan<NY>::kWorkBytes > LPlan<NZ>::kWorkBytes ? SPlan<NY>::kWorkBytes : LPlan<NZ>::kWorkBytes;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  cpx<float>* const dense0 = reinterpret_cast<cpx<float>*>(smem_raw);
-  constexpr int kDenseElems = kTileBytes / 8;
-  cpx<float>* const work = reinterpret_cast<cpx<float>*>(smem_raw + 2 * kTileBytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + 2 * kTileBytes + kWork);
-  uint64_t* full = bars;
-  uint64_t* done = bars + 2;
-  volatile int* desc = reinterpret_cast<volatile int*>(bars + 8);   // [2][4]: type, plane, idx
-  // The acquire loads / release reductions of the copy warp invalidate L1 (CCTL.IVALL), so the
-  // per-tile twiddle reloads of the FFT warps come from shared-memory copies of the tables.
-  cpx<float>* const tw2s = reinterpret_cast<cpx<float>*>(smem_raw + 2 * kTileBytes + kWork + 2 * kBarBytes);
-  cpx<float>* const twHs = tw2s + NY;
-  cpx<float>* const twNs = twHs + NZ / 2;
-  const int tid = threadIdx.x;
-  if (tid == 0) {
-    mbar_init(&full[0], 1);
-    mbar_init(&full[1], 1);
-    mbar_init(&done[0], kConsumers);
-    mbar_init(&done[1], kConsumers);
-    fence_barrier_init();
-  }
-  for (int q = tid; q < NY; q += kThreads) tw2s[q] = ldg_cpx(p.k2.tw + q);
-  for (int q = tid; q < NZ / 2; q += kThreads) {
-    twHs[q] = ldg_cpx(p.k3.twH + q);
-    twNs[q] = ldg_cpx(p.k3.twN + q);
-  }
-  __syncthreads();
-
-  if (tid >= kConsumers) {
-    if (tid == kConsumers) {
-      tma_prefetch_desc(&map_in);
-      tma_prefetch_desc(&map_out);
-      char* gbase = reinterpret_cast<char*>(p.k3.buf);
-      // planes of the last kSigLag K2 stores, not yet signalled (store completion is only waited
-      // for kSigLag tiles later, so the copy warp never stalls on HBM write latency)
-      constexpr int kSigLag = 4;
-      int pend[kSigLag];
-#pragma unroll
-      for (int q = 0; q < kSigLag; ++q) pend[q] = -1;
-      auto signal = [&](int plane) {
-        if (plane >= 0) {
-          asm volatile("fence.proxy.async;" ::: "memory");
-          asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.plane_done + plane) : "memory");
-        }
-      };
-      auto flush_signals = [&]() {
-        bulk_wait0();
-#pragma unroll
-        for (int q = 0; q < kSigLag; ++q) { signal(pend[q]); pend[q] = -1; }
-      };
-      int cur_type[2], cur_plane[2], cur_idx[2];
-      bool deferred[2] = {false, false};
-      auto plane_ready = [&](int plane) -> bool {
-        unsigned int have;
-        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(have) : "l"(p.plane_done + plane) : "memory");
-        return have >= (unsigned)p.t2;
-      };
-      auto publish = [&](int b, int type, int plane, int idx) {
-        cur_type[b] = type; cur_plane[b] = plane; cur_idx[b] = idx;
-        desc[4 * b + 0] = type; desc[4 * b + 1] = plane; desc[4 * b + 2] = idx;
-      };
-      // issues the load of the tile published for buffer b.  A K3 tile needs its plane's y pass
-      // complete (`ready` = already known to be).  Non-blocking: returns false if it is not; the
-      // caller retries, blocking, once every earlier tile of this CTA has been stored and
-      // signalled -- see the main loop.
-      auto load = [&](int b, bool blocking, bool ready) -> bool {
-        const int type = cur_type[b], plane = cur_plane[b], idx = cur_idx[b];
-        if (type == kTileEnd) {
-          mbar_arrive(&full[b]);
-        } else if (type == kTileK2) {
-          const int z0 = idx * P2::TZ;
-          mbar_expect_tx(&full[b], (uint32_t)P2::kDenseBytes);
-          for (int r0 = 0; r0 < NY; r0 += p.k2.box_rows) {
-            const int src = r0 / p.k2.rows_per_src, rl = r0 - src * p.k2.rows_per_src;
-            tma_load_4d(dense0 + b * kDenseElems + r0 * P2::TZ, &map_in, &full[b], 2 * z0, rl, plane, src);
-          }
-        } else {
-          if (!ready) ready = plane_ready(plane);
-          if (!ready && !blocking) return false;
-          while (!ready) {
-            __nanosleep(100);
-            ready = plane_ready(plane);
-          }
-          asm volatile("fence.proxy.async;" ::: "memory");
-          const size_t off = ((size_t)plane * p.t3 + idx) * (size_t)P3::kDenseBytes;
-          mbar_expect_tx(&full[b], (uint32_t)P3::kDenseBytes);
-          bulk_g2s(dense0 + b * kDenseElems, gbase + off, (uint32_t)P3::kDenseBytes, &full[b]);
-        }
-        return true;
-      };
-      // static schedule: this CTA owns tickets blockIdx.x + n*gridDim.x, in increasing order
-      unsigned int ticket = blockIdx.x;
-      {
-        int type, plane, idx;
-        k23_decode(p, ticket, type, plane, idx);
-        ticket += gridDim.x;
-        publish(0, type, plane, idx);
-        load(0, true, false);          // nothing of ours is pending: blocking is safe
-        k23_decode(p, ticket, type, plane, idx);
-        ticket += gridDim.x;
-        publish(1, type, plane, idx);
-        deferred[1] = !load(1, false, false);
-      }
-      for (int i = 0;; ++i) {
-        const int b = i & 1;
-        if (cur_type[b] == kTileEnd) break;
-        if (deferred[b]) {
-          // every earlier tile of this CTA has been stored; make that visible, then wait
-          flush_signals();
-          load(b, true, false);
-          deferred[b] = false;
-        }
-        // claim the tile that will replace this one while the FFT warps are still busy with it:
-        // the ticket round trip and the dependency probe stay off the critical path
-        int ntype, nplane, nidx;
-        k23_decode(p, ticket, ntype, nplane, nidx);
-        ticket += gridDim.x;
-        // dependency probe issued now, looked at after the wait below (latency hidden)
-        unsigned int nhave = 0;
-#ifdef RF_EXP_NOSIG
-        nhave = 1u << 30;
-#else
-        if (ntype == kTileK3)
-          asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(nhave) : "l"(p.plane_done + nplane) : "memory");
-#endif
-        mbar_wait(&done[b], (i >> 1) & 1);
-        const bool nready = ntype != kTileK3 || nhave >= (unsigned)p.t2;
-        const int stored_plane = cur_type[b] == kTileK2 ? cur_plane[b] : -1;
-        if (cur_type[b] == kTileK2) {
-          const int z0 = cur_idx[b] * P2::TZ;
-          for (int r0 = 0; r0 < NY; r0 += P2::kBoxRows)
-            tma_store_3d(&map_out, dense0 + b * kDenseElems + r0 * P2::TZ, 2 * z0, r0, cur_plane[b]);
-        } else {
-          const size_t off = ((size_t)cur_plane[b] * p.t3 + cur_idx[b]) * (size_t)P3::kDenseBytes;
-          bulk_s2g(gbase + off, dense0 + b * kDenseElems, (uint32_t)P3::kDenseBytes);
-        }
-        bulk_commit();
-        bulk_wait_read0();
-        publish(b, ntype, nplane, nidx);
-        deferred[b] = !load(b, false, nready);
-        // the store committed kSigLag tiles ago is complete once at most kSigLag groups are pending
-#ifndef RF_EXP_NOSIG
-        asm volatile("cp.async.bulk.wait_group %0;" ::"n"(kSigLag) : "memory");
-        signal(pend[0]);
-#endif
-#pragma unroll
-        for (int q = 0; q + 1 < kSigLag; ++q) pend[q] = pend[q + 1];
-        pend[kSigLag - 1] = stored_plane;
-      }
-      flush_signals();
-    }
-    return;
-  }
-
-  // ===== FFT warps =====
-  double s1 = 0.0, s2 = 0.0;
-  const float* zs = p.k3.zscale;
-  for (int i = 0;; ++i) {
-    const int b = i & 1;
-    cpx<float>* const D = dense0 + b * kDenseElems;
-    mbar_wait(&full[b], (i >> 1) & 1);
-    const int type = desc[4 * b + 0];
-    if (type == kTileEnd) break;
-    if (type == kTileK2) {
-      cpx<float> twr[P2::R1];
-      load_step_twiddles_smem<P2::R1>(twr, tw2s, tid / P2::TZ);
-      k2_tile_body<NY>(D, work, tid, twr);
-    } else {
-      cpx<float> twr[P3::R1];
-      cpx<float> twu[K3Consts<NZ>::kPairsPerThread];
-      sfor<0, K3Consts<NZ>::kPairsPerThread>([&](auto qi) {
-        constexpr int q = decltype(qi)::value;
-        twu[q] = ld_cpx(twNs + (tid + q * kConsumers) % (P3::H / 2));
-      });
-      load_step_twiddles_smem<P3::R1>(twr, twHs, tid % P3::M);   // (NZ <= 2048 here: SPLIT == 1)
-      cpx<float> a1 = {0.f, 0.f}, a2 = {0.f, 0.f};
-      k3_tile_body<NZ>(D, work, tid, twr, twu, zs, a1, a2, p.k3.twH);
-      s1 += (double)a1.x + (double)a1.y;
-      s2 += (double)a2.x + (double)a2.y;
-    }
-    fence_proxy_async();
-    mbar_arrive(&done[b]);
-    ConsumerSync()();
-  }
-
-  if (p.k3.partials) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-    }
-    __shared__ double red[2][kConsumers / 32];
-    const int wid = tid >> 5, lane = tid & 31;
-    if (lane == 0) { red[0][wid] = s1; red[1][wid] = s2; }
-    ConsumerSync()();
-    if (tid == 0) {
-      double t1 = 0, t2 = 0;
-      for (int q = 0; q < kConsumers / 32; ++q) { t1 += red[0][q]; t2 += red[1][q]; }
-      p.k3.partials[2 * (size_t)blockIdx.x] = t1;
-      p.k3.partials[2 * (size_t)blockIdx.x + 1] = t2;
-    }
-  }
 }
 
 // @@PIPE_END@@

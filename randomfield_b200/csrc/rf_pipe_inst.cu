@@ -83,6 +83,24 @@ bool PipeLaunch<N>::k1q_fits(int hinge_cells) {
   // two CTAs (+1 KB reserved each) inside the 228 KB of an SM
   return pipe::k1q_smem_bytes<N>(hinge_cells) <= 112 * 1024;
 }
+template <bool INJ, bool POT>
+static int launch_k1r(const pipe::K1PMaps& out, const pipe::K1PParams& p, int grid, cudaStream_t s) {
+  const int smem = pipe::k1r_smem_bytes<N>(INJ ? 0 : p.tab.lut_n);
+  int e;
+  if ((e = set_smem_pipe(pipe::k1r_generate_xfft<N, INJ, POT>, smem))) return e;
+  pipe::k1r_generate_xfft<N, INJ, POT><<<grid, pipe::kThreadsR, smem, s>>>(out, p);
+  return (int)cudaGetLastError();
+}
+template <>
+int PipeLaunch<N>::k1r(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p,
+                       int grid, cudaStream_t s) {
+  if (injected) return potential ? launch_k1r<true, true>(out, p, grid, s) : launch_k1r<true, false>(out, p, grid, s);
+  return potential ? launch_k1r<false, true>(out, p, grid, s) : launch_k1r<false, false>(out, p, grid, s);
+}
+template <>
+bool PipeLaunch<N>::k1r_fits(int hinge_cells) {
+  return pipe::k1r_smem_bytes<N>(hinge_cells) <= 226 * 1024;
+}
 template <>
 int PipeLaunch<N>::tile_cols() {
   return pipe::SPlan<N>::TZ;
@@ -133,6 +151,15 @@ int PipeLaunch<N>::k1q(bool injected, bool potential, const pipe::K1PMaps& out, 
 }
 template <>
 bool PipeLaunch<N>::k1q_fits(int) {
+  return false;
+}
+template <>
+int PipeLaunch<N>::k1r(bool injected, bool potential, const pipe::K1PMaps& out, const pipe::K1PParams& p,
+                       int grid, cudaStream_t s) {
+  return k1p(injected, potential, out, p, grid, s);
+}
+template <>
+bool PipeLaunch<N>::k1r_fits(int) {
   return false;
 }
 template <>

@@ -11,7 +11,10 @@ run as CUDA kernels in librf_b200.so.  Differences a user can observe:
   ``generator.potential`` materialises the reference's array on first access;
 * returned arrays are views of one page-locked host buffer that later calls overwrite (the
   reference returns views of its single work buffer with the same caveat); the device copy
-  is available zero-copy through :meth:`device_field`.
+  is available zero-copy through :meth:`device_field`.  The lensing potential is a separate
+  array, as in the reference (generate.py:398-399);
+* extensions: ``dtype=`` (float64 arithmetic), :meth:`set_white_noise`, :meth:`measure_power`
+  (the forward r2c transform the reference plans but never runs + shell-binned P(k)).
 """
 from __future__ import print_function, division
 
@@ -123,15 +126,40 @@ class Generator(object):
     (anything with the astropy FLRW attributes used here), optional tabulated ``power`` and
     ``verbose``.  ``dtype`` (extension, default float32 like the reference's complex64 plan)
     selects float64 arithmetic.
+
+    ``group`` (extension) slab-decomposes the grid over the ranks of a ``torch.distributed``
+    process group (``True``: the default group; one process per GPU, launched with torchrun):
+    every rank constructs the Generator with the same arguments, the methods are collective, and
+    each returns this rank's x-slab ``[rank * nx/G, (rank + 1) * nx/G)`` of the reference's array
+    -- concatenating the ranks' results along axis 0 gives the single-GPU array bit for bit.
+    ``delta_field_rms`` is the rms of the whole field.  :meth:`gather` collects a result on rank 0.
     """
 
     def __init__(self, nx, ny, nz, grid_spacing_Mpc_h, num_plot_sections=4,
-                 cosmology=None, power=None, verbose=False, dtype=np.float32):
+                 cosmology=None, power=None, verbose=False, dtype=np.float32, group=None):
         if nx % 2 or ny % 2 or nz % 2:
             raise ValueError('All shape dimensions must be even.')
-        self._engine = _lib.Engine(nx, ny, nz, dtype=dtype)
+        self._slab = None
+        self._group = None
+        if group is not None and group is not False:
+            import torch.distributed as dist
+            if not dist.is_initialized():
+                raise RuntimeError('group= needs an initialised torch.distributed process group.')
+            self._group = None if group is True else group
+            if dist.get_world_size(self._group) > 1:
+                from .slab import SlabEngine
+                if power is None and cosmology is None:
+                    power = powertools.load_default_power()
+                if power is None:
+                    raise RuntimeError('power.calculate_power requires classy.')
+                self._slab = SlabEngine(nx, ny, nz, grid_spacing_Mpc_h, powertools.validate_power(power),
+                                        dtype=dtype, group=self._group)
+                self._engine = self._slab.engine
+        if self._slab is None:
+            self._engine = _lib.Engine(nx, ny, nz, dtype=dtype)
         self._real_dtype = self._engine.real_dtype
         self._shape = (nx, ny, nz)
+        self._local_shape = self._engine.field_shape
         itemsize = self._engine.complex_dtype.itemsize
         self.plan_c2r = _PlanView(self, True, nx * ny * (nz // 2 + 1) * itemsize)
         self.plan_r2c = _PlanView(self, False, 0)
@@ -142,8 +170,10 @@ class Generator(object):
         self._potential_cache = None
         self._noise = None
         self._host = None
+        self._host_psi = None
         self._field_kind = None
         self._last = None
+        self._table_key = None
 
         if nz % num_plot_sections != 0:
             raise ValueError('Z-axis does not evenly divided into {0} plot sections.'
@@ -189,18 +219,56 @@ class Generator(object):
                   ' = {0:.4f} deg**2 field of view.'.format(self.x_fov * self.y_fov))
 
     # ------------------------------------------------------------------ host/device views
+    def _host_buffer(self):
+        if self._host is None:
+            self._host = _lib.PinnedArray(self._local_shape, self._real_dtype)
+        return self._host.array
+
     def _host_field(self):
         """Host copy of the device real field in the generator's page-locked buffer."""
-        if self._host is None:
-            self._host = _lib.PinnedArray(self._shape, self._real_dtype)
-        self._engine.copy_field(self._host.array)
-        return self._host.array
+        out = self._host_buffer()
+        self._engine.copy_field(out)
+        return out
 
     def _host_kspace(self):
         if self._last is None:
             raise RuntimeError('No k-space field has been generated yet.')
-        seed, _ = self._last
+        seed, smoothing = self._last
+        self._load_table(smoothing)
         return self._engine.kspace_public(seed, potential=False)
+
+    def _run(self, seed, potential, zscale, want_stats, out):
+        """seed -> real-space field (this rank's x-slab) streamed into the host array `out`."""
+        if self._slab is not None:
+            self._slab.generate(seed, potential=potential, zscale=zscale, want_stats=want_stats)
+            self._engine.copy_rows(out, 0, wait=False)
+        else:
+            # pass 1, then passes 2 + 3 range by range with each range's device -> host copy under
+            # way while the next range is transformed (rf_finish_yz_streamed)
+            self._engine.generate_xpass(seed, potential=potential)
+            self._engine.finish_yz_streamed(out, zscale=zscale, want_stats=want_stats)
+
+    @property
+    def x_slab(self):
+        """[lo, hi) of axis 0 held by this rank (the whole axis on one GPU)."""
+        nxl = self._local_shape[0]
+        return self._engine.rank * nxl, (self._engine.rank + 1) * nxl
+
+    def gather(self, local, dst=0):
+        """Collect the ranks' x-slabs of a result on rank `dst`: returns the (nx, ny, nz) array
+        there and None elsewhere (the array itself on one GPU)."""
+        if self._slab is None:
+            return local
+        import torch
+        import torch.distributed as dist
+        rank, world = dist.get_rank(self._group), dist.get_world_size(self._group)
+        mine = torch.from_numpy(np.ascontiguousarray(local)).cuda()
+        parts = [torch.empty_like(mine) for _ in range(world)] if rank == dst else None
+        dist.gather(mine, parts, dst=dist.get_global_rank(self._group, dst) if self._group is not None else dst,
+                    group=self._group)
+        if rank != dst:
+            return None
+        return np.concatenate([t.cpu().numpy() for t in parts], axis=0)
 
     def device_field(self):
         """The current real field as a torch CUDA tensor sharing the library's memory."""
@@ -209,8 +277,20 @@ class Generator(object):
     def set_white_noise(self, noise):
         """Inject white noise: ``2*nx*ny*(nz//2+1)`` float64 standard-normal deviates in the
         order ``RandomState.normal(size)`` fills the reference's buffer (random.py:17-28).
-        ``None`` returns to the Philox generator."""
-        self._engine.set_noise(noise)
+        ``noise`` is the whole array, or an iterable of consecutive slabs of x rows (each
+        ``(n, ny, nz//2+1, 2)`` or flat) that is uploaded slab by slab -- 16 bytes per mode never
+        have to exist on the host at once (random.py:25-27).  ``None`` returns to the Philox
+        generator."""
+        if noise is None or isinstance(noise, np.ndarray):
+            self._engine.set_noise(noise)
+        else:
+            x0, per_row = 0, 2 * self._shape[1] * (self._shape[2] // 2 + 1)
+            for slab in noise:
+                slab = np.ascontiguousarray(slab, dtype=np.float64).reshape(-1)
+                self._engine.set_noise_rows(slab, x0)
+                x0 += slab.size // per_row
+            if x0 != self._shape[0]:
+                raise ValueError('noise slabs cover {0} of {1} x rows.'.format(x0, self._shape[0]))
         self._noise = noise is not None
 
     @property
@@ -220,15 +300,32 @@ class Generator(object):
         if self._potential_args is None:
             return None
         if self._potential_cache is None:
+            # generated into scratch memory on the device: no side effect on the field
             self._load_table(self._potential_args[1])
             self._potential_cache = self._engine.kspace_public(self._potential_args[0], potential=True)
-            self._field_kind = None
         return self._potential_cache
 
     def _load_table(self, smoothing):
+        # the device table is rebuilt only when the smoothing (or the power array) changes
+        key = (float(smoothing), id(self.power))
+        if key == self._table_key:
+            return
         self.smoothed_power = powertools.filter_power(self.power, smoothing)
         k, sigma = powertools.sigma_table(self.smoothed_power, self._shape, self.grid_spacing_Mpc_h)
         self._engine.set_power(k, sigma, self.grid_spacing_Mpc_h)
+        self._table_key = key
+
+    def measure_power(self, k_edges=None, nbins=24):
+        """Shell-averaged power spectrum of the current real-space field, measured on the device
+        with the forward r2c transform (the reference's ``plan_r2c``, generate.py:79-80): returns
+        ``(k_edges, Pk, n_modes)`` with Pk in (Mpc/h)^3.  Extension of the reference API."""
+        if self._field_kind is None:
+            raise RuntimeError('No field in the buffer.')
+        if k_edges is None:
+            k_edges = np.linspace(self.k_min, np.pi / self.grid_spacing_Mpc_h, nbins + 1)
+        k_edges = np.asarray(k_edges, dtype=np.float64)
+        pk, cnt = self._engine.r2c_power(k_edges)
+        return k_edges, pk, cnt
 
     # ------------------------------------------------------------------ the hot path
     def generate_delta_field(self, smoothing_length_Mpc_h=0., seed=None,
@@ -239,18 +336,30 @@ class Generator(object):
         generator's host buffer that later calls overwrite."""
         if seed is None:
             seed = int.from_bytes(os.urandom(8), 'little')
+            if self._slab is not None:      # every rank must draw the same field
+                import torch
+                import torch.distributed as dist
+                t = torch.tensor([seed >> 1], dtype=torch.int64, device='cuda')
+                dist.broadcast(t, src=dist.get_global_rank(self._group, 0) if self._group is not None else 0,
+                               group=self._group)
+                seed = int(t.item())
         self._load_table(smoothing_length_Mpc_h)
-        self._engine.generate_delta(seed, potential=False, zscale=None, want_stats=True)
-        s1, s2, n = self._engine.stats()
-        mean = s1 / n
-        self.delta_field_rms = self._real_dtype.type(np.sqrt(max(s2 / n - mean * mean, 0.)))
+        delta = self._host_buffer()
+        self._run(seed, False, None, True, delta)
+        if self._slab is not None:
+            _, std = self._slab.global_stats()     # one 3-double all-reduce
+            self.delta_field_rms = self._real_dtype.type(std)
+        else:
+            s1, s2, n = self._engine.stats()
+            mean = s1 / n
+            self.delta_field_rms = self._real_dtype.type(np.sqrt(max(s2 / n - mean * mean, 0.)))
         self._last = (seed, smoothing_length_Mpc_h)
         self._potential_args = (seed, smoothing_length_Mpc_h) if save_potential else None
         self._potential_cache = None
         self._field_kind = 'delta'
         if self.verbose:
             print('Delta field has standard deviation {0:.3f}.'.format(self.delta_field_rms))
-        delta = self._host_field()
+        self._engine.copy_wait()
         if show_plot or save_plot_name is not None:
             self.plot_slice(show_plot=show_plot, save_plot_name=save_plot_name,
                             clip_symmetric=True, label='Matter inhomogeneity ' +
@@ -284,9 +393,10 @@ class Generator(object):
         if light_cone:
             zscale = zscale * self.growth_function / (1 + self.redshifts)
         self._load_table(smoothing)
-        self._engine.generate_delta(seed, potential=True, zscale=zscale, want_stats=False)
+        field = self._host_buffer()
+        self._run(seed, True, zscale, False, field)
         self._field_kind = 'potential'
-        field = self._host_field()
+        self._engine.copy_wait()
         if show_plot or save_plot_name is not None:
             self.plot_slice(clip_symmetric=True, show_plot=show_plot, save_plot_name=save_plot_name,
                             label='Newtonian potential $\\Phi(r)$ [s$^{-2}$]')
@@ -295,20 +405,22 @@ class Generator(object):
     def calculate_lensing_potential(self, i_min=None, show_plot=False, save_plot_name=None):
         """Lensing potential psi(r) (generate.py:353-418): for every slice the Simpson integral
         over comoving distance of -2 (cotK(D) - cotK(D_src)) dPhi, truncated below DC[i_min]
-        (default nz // 32).  Runs in place on the device field, which normally holds the
-        light-cone Newtonian potential (call calculate_newtonian_potential first); the returned
-        array is the host view of that buffer, as for the other results."""
+        (default nz // 32).  Integrates the Newtonian potential held by the device field (call
+        calculate_newtonian_potential first) into a separate array, as the reference does
+        (generate.py:398-399): the potential and the host array returned for it stay intact, and
+        the call can be repeated with another i_min."""
         nDC = self.DC.size
         if i_min is None:
             i_min = nDC // 32
         if i_min < 0 or i_min >= nDC:
             raise ValueError(
                 'Invalid i_min {}. Expected 0 - {}.'.format(i_min, nDC - 1))
-        if self._field_kind is None:
-            raise RuntimeError('No field to integrate: generate a potential first.')
+        if self._field_kind != 'potential':
+            raise RuntimeError('No Newtonian potential in the buffer: call calculate_newtonian_potential first.')
         self._engine.lensing(i_min, lensing_tables(self.DC, cot_k(self.DC, self.DA, self.cosmology.Ok0)))
-        self._field_kind = 'lensing'
-        field = self._host_field()
+        if self._host_psi is None:
+            self._host_psi = _lib.PinnedArray(self._local_shape, self._real_dtype)
+        field = self._engine.copy_rows(self._host_psi.array, 0, which=_lib.RF_BUF_AUX)
         if show_plot or save_plot_name is not None:
             self.plot_slice(field=field, clip_percent=15.0, clip_symmetric=True, show_plot=show_plot,
                             save_plot_name=save_plot_name,

@@ -92,27 +92,11 @@ def test_potential_and_zscale_across_decompositions():
     assert np.array_equal(got, ref)
 
 
-def test_fused_pass12_kernel_matches(monkeypatch):
-    """The opt-in fused pass-1 + pass-2 kernel (RF_FUSE12=1, rf_fuse12.cuh).  Its pass-2 warp group
-    runs a radix 16x8x8 plan where k2p runs 32x32, so the field agrees to rounding (rel. RMS
-    <= 1e-6), not bit for bit: one more reason it stays opt-in."""
-    from randomfield_b200 import slab
-    power = oracle.load_default_power()
-    shape = (512, 512, 64)
-    for potential in (False, True):
-        monkeypatch.setenv("RF_FUSE12", "0")
-        ref, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1, potential=potential)
-        monkeypatch.setenv("RF_FUSE12", "1")
-        got, _, _ = slab.run_virtual_slabs(*shape, 2.0, power, seed=5, world=1, potential=potential)
-        err = np.sqrt(np.mean((got.astype(np.float64) - ref) ** 2)) / ref.std(dtype=np.float64)
-        assert err <= 1e-6
-
-
-@pytest.mark.parametrize("mode", ["1", "2"])
+@pytest.mark.parametrize("mode", ["2"])
 @pytest.mark.parametrize("shape", [(64, 256, 256), (128, 1024, 128), (64, 64, 2048), (256, 512, 1024)])
 def test_fused_yz_kernels_bit_identical(monkeypatch, mode, shape):
-    """Opt-in fused pass-2 + pass-3 kernels (RF_FUSE=1: k23p, two-buffer ring; RF_FUSE=2: k23q,
-    in-place tiles in a three-deep ring): same arithmetic in the same order as k2p + k3q."""
+    """Fused pass-2 + pass-3 kernel (RF_FUSE=2: k23q, in-place tiles in a three-deep ring) wherever
+    it fits: same arithmetic in the same order as k2p + k3q."""
     from randomfield_b200 import slab
     power = oracle.load_default_power()
     zs = np.linspace(0.5, 1.5, shape[2])
@@ -172,3 +156,35 @@ def test_nccl_two_ranks_matches_single(tmp_path, direct):
     assert np.array_equal(got, ref)
     std = float(open(os.path.join(out, "std.txt")).read())
     assert abs(std - std1) <= 1e-9 * std1
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs two GPUs")
+def test_generator_over_two_ranks(tmp_path):
+    """randomfield_b200.Generator(group=True) under torchrun (generate.py:74-75,144-146,232-233,
+    282-283,353-354 slab-decomposed): the ranks' delta, rho, Phi and psi slabs concatenated along
+    axis 0 equal the single-GPU Generator's arrays bit for bit, and delta_field_rms agrees."""
+    import randomfield_b200 as rf
+    shape = (256, 256, 128)
+    script = os.path.join(ROOT, "tests", "multi_worker_gen.py")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", "29541", script, str(tmp_path),
+           ",".join(map(str, shape))]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    parts = [np.load(os.path.join(str(tmp_path), "gen_rank%d.npz" % k)) for k in range(2)]
+    gen = rf.Generator(*shape, 2.0)
+    delta = gen.generate_delta_field(seed=77, smoothing_length_Mpc_h=1.0).copy()
+    assert np.array_equal(np.concatenate([p["delta"] for p in parts], axis=0), delta)
+    assert abs(float(parts[0]["rms"]) - float(gen.delta_field_rms)) <= 1e-6 * float(gen.delta_field_rms)
+    assert float(parts[0]["rms"]) == float(parts[1]["rms"])
+    # the density uses the rms: equal to float32 rounding of the table built from it
+    rho = gen.convert_delta_to_density().copy()
+    got = np.concatenate([p["rho"] for p in parts], axis=0)
+    assert np.all(np.abs(got - rho) <= 2e-6 * rho)
+    phi = gen.calculate_newtonian_potential(light_cone=True).copy()
+    assert np.array_equal(np.concatenate([p["phi"] for p in parts], axis=0), phi)
+    assert np.array_equal(parts[0]["phi_gathered"], phi)
+    psi = gen.calculate_lensing_potential(i_min=3).copy()
+    assert np.array_equal(np.concatenate([p["psi"] for p in parts], axis=0), psi)
+    assert np.array_equal(np.concatenate([p["phi_after"] for p in parts], axis=0), phi)
+    assert [tuple(p["x_slab"]) for p in parts] == [(0, 128), (128, 256)]

@@ -90,6 +90,10 @@ INJECT_CASES = [
     ((128, 64, 256), 2.0, 0.0, np.float32, 5),
     ((256, 256, 256), 2.0, 4.0, np.float32, 123),     # BASELINE config 2
     ((256, 256, 256), 2.0, 4.0, np.float64, 123),     # BASELINE config 2, float64 mode
+    ((1024, 64, 64), 2.0, 0.0, np.float32, 21),       # 1024-point x pass (k1q<1024>, injected branch)
+    ((64, 1024, 128), 2.0, 0.0, np.float32, 22),      # 1024-point y pass (k2p<1024>)
+    ((64, 64, 1024), 2.0, 1.0, np.float32, 23),       # 1024-point z pass (k3q<1024>)
+    ((512, 512, 64), 2.0, 0.0, np.float32, 24),       # 512-point x and y passes
     ((12, 10, 8), 2.5, 0.0, np.float32, 9),           # generic (non power-of-two) path
     ((16, 8, 12), 2.5, 1.0, np.float64, 7),
 ]
@@ -205,39 +209,63 @@ def test_gaussian_variance_kat_gpu(lib):
     assert abs(np.mean(var) - calc) < 0.01 * calc
 
 
-def test_power_spectrum_recovered(lib):
-    """Measured P(k) of the generated field recovers the input spectrum within cosmic
-    variance: |delta_k|^2 V / N^6 averaged over shells of N_modes modes scatters around P(k)
-    with relative std 1/sqrt(N_modes)."""
-    shape, spacing, seed = (128, 128, 128), 2.0, 2025
-    power = oracle.load_default_power()
-    eng = _engine(lib, shape, spacing, power)
-    eng.generate_delta(seed)
-    delta = eng.copy_field().astype(np.float64)
-    nx, ny, nz = shape
+def _numpy_shell_power(delta, spacing, edges):
+    """The checker of rf_r2c_power: np.fft.rfftn + shell binning on the host (full k-space
+    average: interior planes count twice, the planes iz in {0, nz/2} once)."""
+    nx, ny, nz = delta.shape
     N3 = nx * ny * nz
     V = N3 * spacing ** 3
-    dk = np.fft.rfftn(delta)
+    dk = np.fft.rfftn(delta.astype(np.float64))
+    kx2, ky2, kz2 = oracle.create_ksq_grids(delta.shape, spacing, packed=True)
+    k = np.sqrt(kx2 + ky2 + kz2)
+    w = np.full(k.shape, 2.0)
+    w[:, :, 0] = 1.0
+    w[:, :, nz // 2] = 1.0
+    which = np.digitize(k, edges) - 1
+    ok = (which >= 0) & (which < len(edges) - 1)
+    sums = np.bincount(which[ok], weights=(w * np.abs(dk) ** 2)[ok], minlength=len(edges) - 1)
+    cnts = np.bincount(which[ok], weights=w[ok], minlength=len(edges) - 1)
+    with np.errstate(invalid='ignore', divide='ignore'):
+        return np.where(cnts > 0, sums / cnts * V / N3 ** 2, 0.0), cnts.astype(np.int64)
+
+
+@pytest.mark.parametrize("shape,dtype", [((128, 128, 128), np.float32), ((64, 128, 256), np.float32),
+                                         ((32, 48, 40), np.float32), ((64, 64, 64), np.float64)])
+def test_power_spectrum_recovered(lib, shape, dtype):
+    """Gate 4: the measured P(k) of the generated field -- forward r2c transform and shell binning
+    on the DEVICE (rf_r2c_power, the reference's unused plan_r2c seam: generate.py:79-80,
+    transform.py:278-301) -- recovers the input spectrum within cosmic variance: the shell average
+    of |delta_k|^2 V / N^6 over N_modes modes scatters around P(k) with relative std
+    sqrt(2 / N_modes).  The numpy estimator on the same field is the checker of the device one."""
+    spacing, seed = 2.0, 2025
+    power = oracle.load_default_power()
+    eng = _engine(lib, shape, spacing, power, dtype=dtype)
+    eng.generate_delta(seed)
+    delta = eng.copy_field()
+    kmin = 2 * np.pi / (spacing * min(shape))
+    edges = np.linspace(1.5 * kmin, np.pi / spacing, 21)
+    pk, cnt = eng.r2c_power(edges)
+    assert np.array_equal(eng.copy_field(), delta)          # the estimator leaves the field alone
+    pk_np, cnt_np = _numpy_shell_power(delta, spacing, edges)
+    assert np.array_equal(cnt, cnt_np)
+    assert np.allclose(pk, pk_np, rtol=2e-5 if dtype == np.float32 else 1e-10)
+    # input spectrum averaged over the same shells (it varies across a shell)
     kx2, ky2, kz2 = oracle.create_ksq_grids(shape, spacing, packed=True)
     k = np.sqrt(kx2 + ky2 + kz2)
+    w = np.full(k.shape, 2.0)
+    w[:, :, 0] = 1.0
+    w[:, :, shape[2] // 2] = 1.0
     pk_in = np.interp(np.log10(np.where(k > 0, k, 1.0)), np.log10(power['k']), power['Pk'])
-    ratio = (np.abs(dk) ** 2 * V / N3 ** 2) / pk_in
-    # interior planes only: modes there are independent complex Gaussians (no Hermitian pairs)
-    sel = np.zeros(k.shape, dtype=bool)
-    sel[:, :, 1:nz // 2] = True
-    edges = np.linspace(k[sel].min(), k[sel].max(), 25)
-    which = np.digitize(k[sel], edges)
-    r = ratio[sel]
-    worst = 0.0
-    for b in range(1, len(edges)):
-        m = which == b
-        nm = int(m.sum())
-        if nm < 50:
-            continue
-        dev = abs(r[m].mean() - 1.0) * np.sqrt(nm)
-        worst = max(worst, dev)
-    assert worst < 5.0, worst
-    assert abs(r.mean() - 1.0) < 5.0 / np.sqrt(r.size)
+    which = np.digitize(k, edges) - 1
+    ok = (which >= 0) & (which < len(edges) - 1)
+    want = np.bincount(which[ok], weights=(w * pk_in)[ok], minlength=len(edges) - 1) / np.maximum(cnt_np, 1)
+    good = cnt > 100
+    assert good.sum() >= 15
+    dev = (pk[good] / want[good] - 1.0) * np.sqrt(cnt[good] / 2.0)
+    assert np.abs(dev).max() < 5.0, dev
+    assert abs(dev.mean()) < 5.0 / np.sqrt(good.sum())
+    with pytest.raises(ValueError):
+        eng.r2c_power([0.1, 0.1, 0.2])
 
 
 # ------------------------------------------------------------------------------------------
@@ -264,3 +292,156 @@ def test_lensing_potential_matches_reference_loop(lib, shape, dtype, i_min):
     assert err <= (2e-6 if dtype == np.float32 else 1e-12), err
     with pytest.raises(ValueError):
         gen.calculate_lensing_potential(i_min=shape[2])
+
+
+# ------------------------------------------------------------------------------------------
+# the kernel instances the headline number is measured on: axes of 512 and
+# 1024 points, separate passes and the fused y + z kernel, against the float64 oracle
+# ------------------------------------------------------------------------------------------
+HEADLINE_SHAPES = [(1024, 64, 128), (64, 1024, 128), (64, 64, 1024), (512, 512, 128), (128, 512, 512),
+                   (1024, 1024, 128), (128, 1024, 1024)]
+
+
+@pytest.mark.parametrize("fuse", ["0", "2"])
+@pytest.mark.parametrize("shape", HEADLINE_SHAPES)
+def test_headline_kernel_instances_match_oracle(lib, monkeypatch, shape, fuse):
+    """k1q<512|1024>, k2p<512|1024>, k3q<512|1024> (RF_FUSE=0) and k23q_fused_yz<NY, NZ> (RF_FUSE=2)
+    against oracle.philox_kfield + numpy's float64 irfftn: rel-RMS <= 1e-5 (transform.py:303-315)."""
+    spacing, seed = 2.0, 31
+    power = oracle.load_default_power()
+    monkeypatch.setenv("RF_FUSE", fuse)
+    eng = _engine(lib, shape, spacing, power)
+    names = eng.kernel_names
+    assert eng.is_pipelined and names[0] in ("k1r_generate_xfft", "k1q_generate_xfft")
+    if fuse == "2" and shape[1] * (shape[2] // 2) * 8 >= 65536:
+        assert eng.fused_yz == 2 and names[1] == names[2] == "k23q_fused_yz"
+    else:
+        assert names[1:] == ("k2p_strided_fft", "k3q_c2r_lines")
+    kf64 = oracle.philox_kfield_big(shape, spacing, power, seed)
+    truth = np.fft.irfftn(kf64, s=shape, axes=(0, 1, 2))
+    eng.generate_delta(seed, want_stats=True)
+    delta = eng.copy_field()
+    assert _relrms(delta, truth) <= TOL_F32
+    assert np.abs(delta - truth).max() <= 2e-5 * np.abs(truth).max()
+    s1, s2, cnt = eng.stats()
+    assert abs(np.sqrt(s2 / cnt - (s1 / cnt) ** 2) - truth.std()) <= 1e-5 * truth.std()
+    eng.close()
+
+
+def _host_ram_gb():
+    try:
+        import psutil
+        return psutil.virtual_memory().available / 2 ** 30
+    except Exception:
+        return 0.0
+
+
+def test_config3_full_1024_cubed(lib):
+    """BASELINE config 3 at its full size through the public API: 1024^3 delta field + lognormal
+    density + light-cone Newtonian potential on one B200, every value compared with the float64
+    oracle evaluated on the host (Philox restatement + scipy's pocketfft c2r in float64).
+    Gate 1 of north_star: rel-RMS <= 1e-5."""
+    import randomfield_b200 as rf
+    import scipy.fft
+    n, spacing, seed = 1024, 2.0, 123
+    if _host_ram_gb() < 48:
+        pytest.skip("needs ~40 GB of host memory for the float64 oracle")
+    shape = (n, n, n)
+    power = oracle.load_default_power()
+    gen = rf.Generator(n, n, n, spacing)
+    delta = gen.generate_delta_field(seed=seed, save_potential=True)
+    assert gen._engine.kernel_names[0] in ("k1r_generate_xfft", "k1q_generate_xfft")   # the benchmarked pass 1
+    assert delta.shape == shape and delta.dtype == np.float32
+    kf = oracle.philox_kfield_big(shape, spacing, power, seed)
+    truth = scipy.fft.irfftn(kf, s=shape, axes=(0, 1, 2), workers=-1, overwrite_x=True)
+    del kf
+    std = truth.std()
+    err2 = 0.0
+    worst = 0.0
+    for x0 in range(0, n, 64):
+        d = delta[x0:x0 + 64].astype(np.float64) - truth[x0:x0 + 64]
+        err2 += float(np.sum(d * d))
+        worst = max(worst, float(np.abs(d).max()))
+    rel = np.sqrt(err2 / truth.size) / std
+    print("1024^3 delta: rel-RMS %.3e, max |err| / std %.3e, rms %.6f (oracle %.6f)"
+          % (rel, worst / std, gen.delta_field_rms, std))
+    assert rel <= TOL_F32
+    assert worst <= 50 * TOL_F32 * std, (rel, worst / std)
+    assert abs(float(gen.delta_field_rms) - std) <= 1e-5 * std
+    # lognormal density (generate.py:266-273) against the oracle applied to the same delta, slab by slab
+    sigma = float(gen.delta_field_rms)
+    want_first = oracle.convert_delta_to_density(delta[:8].astype(np.float64), gen.growth_function,
+                                                 gen.mean_matter_density, sigma, lognormal=True)
+    want_last = oracle.convert_delta_to_density(delta[-8:].astype(np.float64), gen.growth_function,
+                                                gen.mean_matter_density, sigma, lognormal=True)
+    rho = gen.convert_delta_to_density(apply_lognormal_transform=True)
+    assert np.all(np.abs(rho[:8] - want_first) <= 5e-6 * want_first)
+    assert np.all(np.abs(rho[-8:] - want_last) <= 5e-6 * want_last)
+    assert rho.min() > 0
+    # Newtonian potential (generate.py:331-343), light cone
+    del truth
+    kf = oracle.philox_kfield_big(shape, spacing, power, seed, potential=True)
+    kf *= -1.5 * oracle.H0_PER_S ** 2 * gen.cosmology.Om0
+    truth = scipy.fft.irfftn(kf, s=shape, axes=(0, 1, 2), workers=-1, overwrite_x=True)
+    del kf
+    truth *= gen.growth_function / (1 + gen.redshifts)
+    phi = gen.calculate_newtonian_potential(light_cone=True)
+    std = truth.std()
+    err2 = 0.0
+    for x0 in range(0, n, 64):
+        d = phi[x0:x0 + 64].astype(np.float64) - truth[x0:x0 + 64]
+        err2 += float(np.sum(d * d))
+    rel = np.sqrt(err2 / truth.size) / std
+    print("1024^3 Phi: rel-RMS %.3e, std %.3e" % (rel, std))
+    assert rel <= TOL_F32
+    assert np.count_nonzero(phi[::16] == 0) == 0
+
+
+# ------------------------------------------------------------------------------------------
+# SURVEY section 8 row f4: streamed output and chunked white-noise injection
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape,dtype,nranges", [((256, 128, 128), np.float32, 4), ((128, 256, 64), np.float32, 3),
+                                                 ((64, 64, 64), np.float64, 4), ((12, 10, 8), np.float32, 2),
+                                                 ((512, 512, 256), np.float32, 8)])
+def test_streamed_finish_bit_identical(lib, shape, dtype, nranges):
+    """rf_finish_yz_streamed (pass 2 + pass 3 per x range, each range's D2H copy overlapping the
+    next range's kernels) delivers the bits of rf_finish_yz + rf_copy_field, and the same rms."""
+    power = oracle.load_default_power()
+    zs = np.linspace(0.5, 1.5, shape[2])
+    eng = _engine(lib, shape, 2.0, power, dtype=dtype)
+    eng.generate_delta(5, zscale=zs, want_stats=True)
+    ref = eng.copy_field()
+    s_ref = eng.stats()
+    host = lib.PinnedArray(shape, dtype)
+    host.array[:] = -1
+    eng.generate_xpass(5)
+    eng.finish_yz_streamed(host.array, zscale=zs, want_stats=True, nranges=nranges)
+    eng.copy_wait()
+    assert np.array_equal(host.array, ref)
+    s = eng.stats()
+    assert abs(s[1] - s_ref[1]) <= 1e-9 * s_ref[1] and s[2] == s_ref[2]
+    rows = np.empty((shape[0] // 2,) + shape[1:], dtype=dtype)
+    eng.copy_rows(rows, shape[0] // 4)
+    assert np.array_equal(rows, ref[shape[0] // 4: shape[0] // 4 + shape[0] // 2])
+
+
+def test_chunked_noise_injection(lib):
+    """rf_set_noise_rows: the white noise uploaded slab by slab (here straight from the generator,
+    64 x rows at a time) gives the field of the whole-array upload, at a grid past 256^3."""
+    shape, spacing, seed = (512, 256, 256), 2.0, 77
+    power = oracle.load_default_power()
+    nx, ny, nz = shape
+    per_row = 2 * ny * (nz // 2 + 1)
+    rs = np.random.RandomState(seed)
+    slabs = [rs.normal(size=64 * per_row) for _ in range(nx // 64)]
+    import randomfield_b200 as rf
+    gen = rf.Generator(*shape, spacing)
+    gen.set_white_noise(iter(slabs))
+    d1 = gen.generate_delta_field(seed=0).copy()
+    gen.set_white_noise(np.concatenate(slabs))
+    d2 = gen.generate_delta_field(seed=0)
+    assert np.array_equal(d1, d2)
+    ref = oracle.generate_delta_field(shape, spacing, power, noise=np.concatenate(slabs))
+    assert _relrms(d1, ref["delta"]) <= TOL_F32
+    with pytest.raises(ValueError):
+        gen.set_white_noise(iter(slabs[:-1]))

@@ -49,11 +49,11 @@ def test_is_hermitian_of_r2c_output(rf):
         plan = Plan(shape=shape, dtype_in=ftype if packed else complex_type(ftype), inverse=False,
                     overwrite=overwrite, packed=packed)
         plan.data_in[:] = np.random.normal(size=plan.data_in.shape)
+        x = plan.data_in.copy()          # (overwrite=True: the output shares the input's memory)
         result = plan.execute()
         assert is_hermitian(result, packed=packed)
         # and it is the right transform: numpy is the reference's own backend (transform.py:266-270)
-        want = np.fft.rfftn(plan.data_in.astype(np.float64)) if packed else np.fft.fftn(
-            plan.data_in.astype(np.complex128))
+        want = np.fft.rfftn(x.astype(np.float64)) if packed else np.fft.fftn(x.astype(np.complex128))
         assert np.allclose(result, want, atol=1e-5 if ftype == np.float32 else 1e-12)
 
 
@@ -74,12 +74,14 @@ def test_symmetrize_matches_reference(rf, golden_dir):
     """Packed and unpacked results of the unmodified reference's symmetrize (golden fixture)."""
     from randomfield_b200.transform import symmetrize
     g = np.load(os.path.join(golden_dir, "ref_symmetrize.npz"))
-    for key in ("packed", "unpacked"):
-        data = g[key + "_in"].copy()
-        symmetrize(data, packed=(key == "packed"))
-        assert np.array_equal(data, g[key + "_out"]), key
-        want = oracle.symmetrize(g[key + "_in"].copy(), packed=(key == "packed"))
-        assert np.array_equal(data, want)
+    for key in ("packed", "full"):
+        for ctype in ("complex64", "complex128"):
+            name = key + "_" + ctype
+            data = g[name + "_in"].copy()
+            symmetrize(data, packed=(key == "packed"))
+            assert np.array_equal(data, g[name + "_out"]), name
+            want = oracle.symmetrize(g[name + "_in"].copy(), packed=(key == "packed"))
+            assert np.array_equal(data, want)
 
 
 def test_c2c_round_trip(rf):
@@ -373,7 +375,7 @@ def test_lognormal_default_sigma_and_axis_tables(rf, dtype):
 def test_density_matches_oracle_on_same_delta(rf, shape3, dtype, lognormal):
     """Generator.convert_delta_to_density (rf_density: density_kernel_v4 when nz % 4 == 0, else
     density_kernel) against generate.py:266-273 applied by the oracle to the SAME delta field."""
-    gen = rf.Generator(*shape3, 2.0, dtype=dtype)
+    gen = rf.Generator(*shape3, 2.0, dtype=dtype, num_plot_sections=2)
     delta = gen.generate_delta_field(seed=31).copy()
     sigma = gen.delta_field_rms
     assert abs(float(sigma) - delta.std(dtype=np.float64)) <= 1e-5 * float(sigma)
