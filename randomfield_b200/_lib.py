@@ -236,6 +236,29 @@ class Engine:
     def copy_wait(self):
         check(lib().rf_copy_wait(self._ctx))
 
+    def iter_rows(self, rows=None, which=RF_BUF_FIELD, stage_bytes=1 << 29):
+        """Stream this rank's real field (or RF_BUF_AUX) to the host in chunks of x rows through two
+        page-locked staging buffers: yields (x0, array) with array a (n, ny, nz) view that stays valid
+        until the next iteration; the copy of chunk k+1 is under way while the caller consumes chunk
+        k.  For slabs too large to page-lock whole (34 GB per rank at 4096^3 on 8 GPUs)."""
+        row_bytes = self.ny * self.nz * self.real_dtype.itemsize
+        if rows is None:
+            rows = max(1, min(self.nxl, stage_bytes // row_bytes))
+        if getattr(self, "_stage_rows", 0) != rows:
+            self._stage = [PinnedArray((rows, self.ny, self.nz), self.real_dtype) for _ in range(2)]
+            self._stage_rows = rows
+        starts = list(range(0, self.nxl, rows))
+        if not starts:
+            return
+        n0 = min(rows, self.nxl - starts[0])
+        self.copy_rows(self._stage[0].array[:n0], starts[0], which=which, wait=False)
+        for k, x0 in enumerate(starts):
+            self.copy_wait()
+            if k + 1 < len(starts):
+                n1 = min(rows, self.nxl - starts[k + 1])
+                self.copy_rows(self._stage[(k + 1) & 1].array[:n1], starts[k + 1], which=which, wait=False)
+            yield x0, self._stage[k & 1].array[:min(rows, self.nxl - x0)]
+
     def r2c_power(self, k_edges):
         """Shell-averaged P(k) of the real-space field (rf_r2c_power): returns (Pk, n_modes)."""
         edges = np.ascontiguousarray(k_edges, dtype=np.float64)

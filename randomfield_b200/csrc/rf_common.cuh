@@ -259,13 +259,15 @@ __host__ __device__ __forceinline__ philox_out philox4x32_10(uint32_t c0, uint32
 }
 
 // Box-Muller: two 32-bit words -> one complex standard-normal deviate (re, im each N(0,1)).
-// u1 = ((wa >> 9) + 0.5) / 2^23 in (0,1); angle = pi * (int32)wb / 2^31 in [-pi, pi).
+// u1 = (wa + 0.5) / 2^32 in (0,1) -- all 32 bits of the word: the radius reaches
+// sqrt(2 * 33 * ln 2) = 6.76 (float32 rounds wa to 24 significant bits, which keeps the exponent,
+// i.e. the resolution of the tail); angle = pi * (int32)wb / 2^31 in [-pi, pi).
 template <typename T>
 __device__ __forceinline__ cpx<T> box_muller(uint32_t wa, uint32_t wb);
 
 // MUFU wrappers with flush-to-zero semantics: a bare MUFU, without the denormal pre/post
 // scaling (FSETP + 2 predicated ops) the non-ftz forms carry.  Every argument on the hot path
-// is a normal number (u1 >= 2^-24, -2 ln u1 >= 1.19e-7, k^2 >= 5.9e-7 up to 4096^3 at 2 Mpc/h),
+// is a normal number or zero (2^-33 <= u1 <= 1, -2 ln u1 = 0 or >= 1.19e-7, k^2 >= 5.9e-7 up to 4096^3 at 2 Mpc/h),
 // for which both forms return the same bits.
 __device__ __forceinline__ float lg2_ftz(float x) {
   float r;
@@ -280,7 +282,9 @@ __device__ __forceinline__ float sqrt_ftz(float x) {
 
 template <>
 __device__ __forceinline__ cpx<float> box_muller<float>(uint32_t wa, uint32_t wb) {
-  float u1 = __int_as_float(0x3f800000u | (wa >> 9)) + (-1.0f + 5.9604644775390625e-8f);
+  // u1 = (wa + 0.5) 2^-32 in (0, 1]: the scaling is exact, so log2(u1) keeps its resolution near
+  // u1 = 1 (small radii); the top 128 values of wa round to u1 = 1, i.e. r = 0
+  float u1 = fmaf(__uint2float_rn(wa), 2.3283064365386963e-10f, 1.1641532182693481e-10f);
   float l2 = lg2_ftz(u1);                                   // MUFU.LG2
   float r2 = l2 * -1.3862943611198906f;                     // -2 ln2 * log2(u1) = -2 ln(u1)
   float r = sqrt_ftz(r2);                                   // MUFU.SQRT
@@ -292,7 +296,7 @@ __device__ __forceinline__ cpx<float> box_muller<float>(uint32_t wa, uint32_t wb
 
 template <>
 __device__ __forceinline__ cpx<double> box_muller<double>(uint32_t wa, uint32_t wb) {
-  double u1 = ((double)(wa >> 9) + 0.5) * (1.0 / 8388608.0);
+  double u1 = ((double)wa + 0.5) * (1.0 / 4294967296.0);
   double r = sqrt(-2.0 * log(u1));
   double s, c;
   sincospi((double)(int32_t)wb * (1.0 / 2147483648.0), &s, &c);

@@ -133,9 +133,12 @@ k23q_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant_
     }
     fence_barrier_init();
   }
-  for (int q = tid; q < NY; q += kThreadsQ) tw2s[q] = ldg_cpx(p.k2.tw + q);
+  // step-twiddle tables in [k1][j] order, W^(j k1) at [k1 * M + j]: the lanes of a warp (consecutive
+  // j) read consecutive words -- indexed as W[j * k1] the per-tile reloads cost 15-20 % of all
+  // shared-memory wavefronts in bank conflicts (ncu, round 2)
+  for (int q = tid; q < NY; q += kThreadsQ) tw2s[q] = ldg_cpx(p.k2.tw + (q % P2::M) * (q / P2::M));
   for (int q = tid; q < NZ / 2; q += kThreadsQ) {
-    twHs[q] = ldg_cpx(p.k3.twH + q);
+    twHs[q] = ldg_cpx(p.k3.twH + (q % P3::M) * (q / P3::M));
     twNs[q] = ldg_cpx(p.k3.twN + q);
   }
   __syncthreads();
@@ -257,12 +260,15 @@ k23q_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant_
     if (type == kTileEnd) break;
     if (type == kTileK2) {
       cpx<float> twr[P2::R1];
-      load_step_twiddles_smem<P2::R1>(twr, tw2s, tid / P2::TZ);
+      sfor<0, P2::R1>([&](auto ki) {
+        constexpr int k1 = decltype(ki)::value;
+        twr[k1] = ld_cpx(tw2s + k1 * P2::M + tid / P2::TZ);
+      });
       k2q_tile_body<NY>(B, tid, twr);
     } else {
       cpx<float> twr[P3::R1], twr2[P3::R1];
       cpx<float> twu[K3Consts<NZ>::kPairsPerThread];
-      k3q_load_twiddles<NZ>(twr, twr2, twu, twHs, twNs, tid, [](const cpx<float>* q) { return ld_cpx(q); });
+      k3q_load_twiddles<NZ, true>(twr, twr2, twu, twHs, twNs, tid, [](const cpx<float>* q) { return ld_cpx(q); });
       cpx<float> a1 = {0.f, 0.f}, a2 = {0.f, 0.f};
       k3q_tile_body<NZ>(B, tid, twr, twr2, twu, zs, a1, a2, p.k3.twH);
       s1 += (double)a1.x + (double)a1.y;

@@ -34,8 +34,9 @@ struct K3Fuse {
 };
 
 // twiddles of this thread for k3q_tile_body: step-A factors of its item(s) and the unpack factor(s).
-// tabH holds exp(2 pi i k / H), tabN exp(2 pi i k / NZ) (global memory or shared-memory copies).
-template <int NZ, class LD>
+// tabH holds exp(2 pi i k / H) -- or, TRANSPOSED, the step table W_H^(j k1) at [k1 * M + j] (SPLIT == 1) --
+// and tabN exp(2 pi i k / NZ) (global memory or shared-memory copies).
+template <int NZ, bool TRANSPOSED = false, class LD>
 __device__ __forceinline__ void k3q_load_twiddles(cpx<float> (&twr)[LPlan<NZ>::R1], cpx<float> (&twr2)[LPlan<NZ>::R1],
                                                   cpx<float> (&twu)[K3Consts<NZ>::kPairsPerThread],
                                                   const cpx<float>* tabH, const cpx<float>* tabN, int tid, LD&& ld) {
@@ -46,8 +47,8 @@ __device__ __forceinline__ void k3q_load_twiddles(cpx<float> (&twr)[LPlan<NZ>::R
     const int j0 = pp, j1 = pp == 0 ? M / 2 : M - pp;
     sfor<0, R1>([&](auto ki) {
       constexpr int k1 = decltype(ki)::value;
-      twr[k1] = ld(tabH + P::SPLIT * j0 * k1);
-      twr2[k1] = ld(tabH + P::SPLIT * j1 * k1);
+      twr[k1] = ld(tabH + (TRANSPOSED ? k1 * M + j0 : P::SPLIT * j0 * k1));
+      twr2[k1] = ld(tabH + (TRANSPOSED ? k1 * M + j1 : P::SPLIT * j1 * k1));
     });
     twu[0] = ld(tabN + (pp == 0 ? M / 2 : pp));
   } else {
@@ -57,7 +58,7 @@ __device__ __forceinline__ void k3q_load_twiddles(cpx<float> (&twr)[LPlan<NZ>::R
     });
     sfor<0, R1>([&](auto ki) {
       constexpr int k1 = decltype(ki)::value;
-      twr[k1] = ld(tabH + P::SPLIT * (tid % M) * k1);
+      twr[k1] = ld(tabH + (TRANSPOSED ? k1 * M + tid % M : P::SPLIT * (tid % M) * k1));
       twr2[k1] = twr[k1];
     });
   }
@@ -314,7 +315,7 @@ __global__ void __launch_bounds__(kThreads, 1) k3q_c2r_lines(const K3PParams p) 
   const float* zs = p.zscale;
   cpx<float> twr[P::R1], twr2[P::R1];
   cpx<float> twu[K3Consts<NZ>::kPairsPerThread];
-  k3q_load_twiddles<NZ>(twr, twr2, twu, p.twH, p.twN, tid, [](const cpx<float>* q) { return ldg_cpx(q); });
+  k3q_load_twiddles<NZ, false>(twr, twr2, twu, p.twH, p.twN, tid, [](const cpx<float>* q) { return ldg_cpx(q); });
   int b = 0, ph = 0;
   for (int t = first; t < p.ntiles; t += step) {
     cpx<float>* const B = buf0 + b * kBufElems;

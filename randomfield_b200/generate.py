@@ -270,6 +270,14 @@ class Generator(object):
             return None
         return np.concatenate([t.cpu().numpy() for t in parts], axis=0)
 
+    def iter_field_rows(self, rows=None):
+        """The current device field (this rank's x-slab) streamed to the host in chunks of x rows
+        through two page-locked staging buffers: yields (global x0, (n, ny, nz) array); each array
+        is valid until the next iteration.  For fields too large to hold on the host at once."""
+        lo = self.x_slab[0]
+        for x0, rows_ in self._engine.iter_rows(rows):
+            yield lo + x0, rows_
+
     def device_field(self):
         """The current real field as a torch CUDA tensor sharing the library's memory."""
         return self._engine.field_tensor()

@@ -210,6 +210,11 @@ class SlabEngine(object):
     def local_field(self):
         return self.engine.copy_field()
 
+    def iter_field_rows(self, rows=None):
+        """This rank's x-slab streamed to the host chunk by chunk (Engine.iter_rows): yields
+        (x0 within the slab, (n, ny, nz) array in page-locked staging memory)."""
+        return self.engine.iter_rows(rows)
+
 
 def run_virtual_slabs(nx, ny, nz, spacing, power, seed, world, smoothing=0.0, dtype=np.float32,
                       potential=False, zscale=None, direct=False, chunks=0, split=None):
