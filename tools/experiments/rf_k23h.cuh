@@ -1,21 +1,26 @@
-// rf_k23h.cuh -- the fused y + z pass with TWO FFT groups on half tiles ("ping-pong").
+// NOT BUILT -- kept as the record of a measured experiment: slower than
+// k23q_fused_yz (2.60 ms against 2.36 ms at 1024^3).  To try it again: copy next to rf_k23q.cuh, include it
+// from rf_launch.h and add the launcher of git show HEAD~:randomfield_b200/csrc/rf_fused_inst.cu.
+//
+// rf_k23h.cuh -- the fused y + z pass on HALF tiles with THREE independent FFT groups.
 //
 // k23q_fused_yz (rf_k23q.cuh) moves a 64 KB tile through shared memory six times (TMA in, load A,
 // store A', load B, store B', TMA out: 3072 cycles of the 128 B/clk port) and spends about 2200
 // FMA-pipe cycles on its butterflies -- and because its eight FFT warps walk through the phases of
-// a tile together, the two add up (ncu, round 2: a tile takes the sum, 5300 cycles, with the
-// shared-memory port 60 % and the FMA pipe 25 % busy).  Here the FFT warps are two groups of four.
-// Every tile is cut in two independent halves, one per group, each in its own half buffer:
-//   y-pass tile [NY][TZ columns]  ->  two dense sub-tiles [NY][TZ/2]   (columns are independent)
-//   z-pass tile [TL lines][NZ/2]  ->  two sets of TL/2 lines            (lines are independent)
-// and the groups hand a token back and forth through named barriers: a group runs butterflies only
-// while it holds the token, and does its shared-memory phases without it.  One group's loads and
-// stores therefore run under the other group's butterflies.  Same arithmetic on the same values in
-// the same order as k2p / k3q / k23q: the field is bit-identical.
-//   bar 1       : all 256 FFT threads (final statistics)
+// a tile together, the two add up, and with two warps per scheduler every dependent-issue and
+// shared-memory latency is exposed (ncu, round 2: each FFT warp issues one instruction every six
+// cycles; shared-memory port 60 %, FMA pipe 25 % busy).  Here the unit of work is HALF a tile,
+//   y pass: [NY][TZ/2 columns] (columns are independent), z pass: TL/2 lines (lines are independent),
+// 32 KB in a ring of SIX half-tile slots, and twelve FFT warps form three groups of four that each
+// take every third half tile and run free of each other: three warps per scheduler, in different
+// phases, so one group's shared-memory sweeps run under another's butterflies; three slots are
+// being transformed while three are in transit.  The step twiddles are read from the shared-memory
+// tables right where they are used (no 64-register twiddle arrays), which is what lets 448
+// threads fit the register file.  Same arithmetic on the same values in the same order as
+// k2p / k3q / k23q: the field is bit-identical.
+//   bar 1       : all FFT threads (final statistics)
 //   bar 2 + g   : the 128 threads of group g
-//   bar 4 + g   : group g may run butterflies (bar.sync by group g, bar.arrive by the other group)
-// Loader / storer warps, tickets, plane counters and the three-deep buffer ring are k23q's.
+// Loader / storer warps, tickets (now per half tile) and plane counters are k23q's.
 #pragma once
 #include "rf_k23q.cuh"
 
@@ -23,6 +28,11 @@ namespace rf {
 namespace pipe {
 
 constexpr int kGroupH = kConsumers / 2;   // 128 threads per FFT group
+
+constexpr int kGroupsH = 3;
+constexpr int kSlotsH = 6;
+constexpr int kFftThreadsH = kGroupsH * kGroupH;      // 384
+constexpr int kThreadsH = kFftThreadsH + 64;          // + loader and storer warps
 
 template <int NY, int NZ>
 struct K23H {
@@ -33,8 +43,8 @@ struct K23H {
   static constexpr int kHalf2 = (NY + P2::R1) * TZh * 8;   // padded y-pass half tile
   static constexpr int kHalf3 = TEh * P3::WP * 8;          // padded z-pass half tile
   static constexpr int kHalf = (((kHalf2 > kHalf3 ? kHalf2 : kHalf3) + 127) / 128) * 128;
-  static constexpr int kBuf = 2 * kHalf;
-  static constexpr int kSmem = 3 * kBuf + 2 * kBarBytes + (NY + NZ) * 8;
+  static constexpr int kDense2 = NY * TZh * 8, kDense3 = TEh * P3::H * 8;   // bytes moved per half tile
+  static constexpr int kSmem = kSlotsH * kHalf + 4 * kBarBytes + (NY + NZ) * 8;
   static constexpr bool kOk = K3Fuse<NZ>::value && P2::TZ >= 8 && (P2::M * TZh == kGroupH) &&
                               (P3::M / 2) * TEh == kGroupH && kSmem <= 227 * 1024;
 };
@@ -43,17 +53,10 @@ struct GroupSync {
   int id;
   __device__ __forceinline__ void operator()() const { named_sync(id, kGroupH); }
 };
-// the butterfly token: strict alternation between the two groups
-struct FmaToken {
-  int mine, other;
-  __device__ __forceinline__ void acquire() const { named_sync(mine, kConsumers); }
-  __device__ __forceinline__ void release() const { named_arrive(other, kConsumers); }
-};
-
 // one y-pass half tile, in place in `B` (dense [N][TZh] at the start of a kHalf buffer); t in [0, 128)
 template <int N>
 __device__ __forceinline__ void k2h_tile_body(cpx<float>* __restrict__ B, int t, const cpx<float>* tws,
-                                              const GroupSync gsync, const FmaToken tok) {
+                                              const GroupSync gsync) {
   using P = SPlan<N>;
   constexpr int R1 = P::R1, R2 = P::R2, M = P::M, TZh = P::TZ / 2, IB = R1 / R2;
   using L = LayoutStridedPad<TZh, M>;
@@ -67,24 +70,15 @@ __device__ __forceinline__ void k2h_tile_body(cpx<float>* __restrict__ B, int t,
       v[m] = ld_cpx(Dp + M * m * TZh);
     });
   }
-  cpx<float> twr[R1];
-  sfor<0, R1>([&](auto ki) {
-    constexpr int k1 = decltype(ki)::value;
-    twr[k1] = ld_cpx(tws + k1 * M + j);
-  });
   gsync();
-  tok.acquire();
   fft_dif<R1, true>(v);
-  sfor<1, R1>([&](auto ki) {
-    constexpr int k1 = decltype(ki)::value;
-    v[brev<R1>(k1)] = cmul(v[brev<R1>(k1)], twr[k1]);
-  });
-  tok.release();
   {
     cpx<float>* wa = B + L::idx2(0, j, c);
     sfor<0, R1>([&](auto ki) {
       constexpr int k1 = decltype(ki)::value;
-      st_cpx(wa + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), v[brev<R1>(k1)]);
+      cpx<float> x = v[brev<R1>(k1)];
+      if constexpr (k1 > 0) x = cmul(x, ld_cpx(tws + k1 * M + j));
+      st_cpx(wa + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), x);
     });
   }
   gsync();
@@ -99,12 +93,10 @@ __device__ __forceinline__ void k2h_tile_body(cpx<float>* __restrict__ B, int t,
     });
   });
   gsync();
-  tok.acquire();
   sfor<0, IB>([&](auto qi) {
     constexpr int q = decltype(qi)::value;
     fft_dif<R2, true>(u[q]);
   });
-  tok.release();
   sfor<0, IB>([&](auto qi) {
     constexpr int q = decltype(qi)::value;
     const int w = t + q * kGroupH;
@@ -121,7 +113,7 @@ __device__ __forceinline__ void k2h_tile_body(cpx<float>* __restrict__ B, int t,
 template <int NZ>
 __device__ __forceinline__ void k3h_tile_body(cpx<float>* __restrict__ B, int t, const cpx<float>* twHt,
                                               const cpx<float>* twN, const float* zs, cpx<float>& a1,
-                                              cpx<float>& a2, const GroupSync gsync, const FmaToken tok) {
+                                              cpx<float>& a2, const GroupSync gsync) {
   using P = LPlan<NZ>;
   constexpr int H = P::H, HE = P::HE, R1 = P::R1, R2 = HE / R1, M = P::M, TEh = P::TE / 2;
   using L = LayoutLinesPad<P::WP, P::M>;
@@ -138,15 +130,8 @@ __device__ __forceinline__ void k3h_tile_body(cpx<float>* __restrict__ B, int t,
     v0[m] = ld_cpx(Lp + j0 + M * m);
     v1[m] = ld_cpx(Lp + j1 + M * m);
   });
-  cpx<float> twr[R1], twr2[R1];
-  sfor<0, R1>([&](auto ki) {
-    constexpr int k1 = decltype(ki)::value;
-    twr[k1] = ld_cpx(twHt + k1 * M + j0);
-    twr2[k1] = ld_cpx(twHt + k1 * M + j1);
-  });
   const cpx<float> wj = ld_cpx(twN + (pp == 0 ? PH : pp));
   gsync();
-  tok.acquire();
   if (pp != 0) {
     sfor<0, R1>([&](auto mi) {
       constexpr int m = decltype(mi)::value;
@@ -185,19 +170,18 @@ __device__ __forceinline__ void k3h_tile_body(cpx<float>* __restrict__ B, int t,
   }
   fft_dif<R1, true>(v0);
   fft_dif<R1, true>(v1);
-  sfor<1, R1>([&](auto ki) {
-    constexpr int k1 = decltype(ki)::value;
-    v0[brev<R1>(k1)] = cmul(v0[brev<R1>(k1)], twr[k1]);
-    v1[brev<R1>(k1)] = cmul(v1[brev<R1>(k1)], twr2[k1]);
-  });
-  tok.release();
   {
     cpx<float>* wp0 = B + L::idx2(0, j0, l);
     cpx<float>* wp1 = B + L::idx2(0, j1, l);
     sfor<0, R1>([&](auto ki) {
       constexpr int k1 = decltype(ki)::value;
-      st_cpx(wp0 + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), v0[brev<R1>(k1)]);
-      st_cpx(wp1 + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), v1[brev<R1>(k1)]);
+      cpx<float> x0 = v0[brev<R1>(k1)], x1 = v1[brev<R1>(k1)];
+      if constexpr (k1 > 0) {
+        x0 = cmul(x0, ld_cpx(twHt + k1 * M + j0));
+        x1 = cmul(x1, ld_cpx(twHt + k1 * M + j1));
+      }
+      st_cpx(wp0 + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), x0);
+      st_cpx(wp1 + (L::idx2(k1, 0, 0) - L::idx2(0, 0, 0)), x1);
     });
   }
   gsync();
@@ -215,7 +199,6 @@ __device__ __forceinline__ void k3h_tile_body(cpx<float>* __restrict__ B, int t,
     });
   });
   gsync();
-  tok.acquire();
   sfor<0, IB>([&](auto qi) {
     constexpr int q = decltype(qi)::value;
     fft_dif<R2, true>(u[q]);
@@ -224,7 +207,6 @@ __device__ __forceinline__ void k3h_tile_body(cpx<float>* __restrict__ B, int t,
       stats_accum(u[q][brev<R2>(k2)], a1, a2);
     });
   });
-  tok.release();
   sfor<0, IB>([&](auto qi) {
     constexpr int q = decltype(qi)::value;
     const int w = t + q * kGroupH;
@@ -243,72 +225,80 @@ __device__ __forceinline__ void k3h_tile_body(cpx<float>* __restrict__ B, int t,
   });
 }
 
-// map_in / map_out: the tensor maps of k23q with the box cut to TZ/2 columns
+// map_in / map_out: the tensor maps of k23q with the box cut to TZ/2 columns.  p.t2 / p.t3 count HALF
+// tiles per plane (twice k23q's), and the plane counters count half-tile stores.
 template <int NY, int NZ>
-__global__ void __launch_bounds__(kThreadsQ, 1)
+__global__ void __launch_bounds__(kThreadsH, 1)
 k23h_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_out,
               const K23Params p) {
   using P2 = SPlan<NY>;
   using P3 = LPlan<NZ>;
   using G = K23H<NY, NZ>;
   static_assert(G::kOk, "k23h: unsupported (NY, NZ)");
-  constexpr int kBufElems = G::kBuf / 8, kHalfElems = G::kHalf / 8;
+  constexpr int kSlotElems = G::kHalf / 8;
   constexpr int TZh = G::TZh;
-  constexpr uint32_t kHalf3Bytes = (uint32_t)G::TEh * P3::H * 8;   // dense z-pass half tile
   extern __shared__ __align__(128) unsigned char smem_raw[];
   cpx<float>* const buf0 = reinterpret_cast<cpx<float>*>(smem_raw);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + 3 * G::kBuf);
-  uint64_t* full = bars;        // [3] tile landed (or end marker published)
-  uint64_t* done = bars + 3;    // [3] both FFT groups finished the tile
-  uint64_t* empty = bars + 6;   // [3] the tile's store has been read out of the buffer
-  volatile int* desc = reinterpret_cast<volatile int*>(bars + 9);   // [3][4]: type, plane, idx
-  cpx<float>* const tw2s = reinterpret_cast<cpx<float>*>(smem_raw + 3 * G::kBuf + 2 * kBarBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + kSlotsH * G::kHalf);
+  uint64_t* full = bars;                  // [6] half tile landed (or end marker published)
+  uint64_t* done = bars + kSlotsH;        // [6] the slot's FFT group finished the half tile
+  uint64_t* empty = bars + 2 * kSlotsH;   // [6] the half tile's store has been read out of the slot
+  volatile int* desc = reinterpret_cast<volatile int*>(bars + 3 * kSlotsH);   // [6][4]: type, plane, idx
+  cpx<float>* const tw2s = reinterpret_cast<cpx<float>*>(smem_raw + kSlotsH * G::kHalf + 4 * kBarBytes);
   cpx<float>* const twHs = tw2s + NY;
   cpx<float>* const twNs = twHs + NZ / 2;
+  static_assert(3 * kSlotsH * 8 + kSlotsH * 16 <= 4 * kBarBytes, "barrier area");
   const int tid = threadIdx.x;
   if (tid == 0) {
-    for (int b = 0; b < 3; ++b) {
+    for (int b = 0; b < kSlotsH; ++b) {
       mbar_init(&full[b], 1);
-      mbar_init(&done[b], kConsumers);
+      mbar_init(&done[b], kGroupH);
       mbar_init(&empty[b], 1);
     }
     fence_barrier_init();
   }
   // step-twiddle tables in [k1][j] order (see k23q)
-  for (int q = tid; q < NY; q += kThreadsQ) tw2s[q] = ldg_cpx(p.k2.tw + (q % P2::M) * (q / P2::M));
-  for (int q = tid; q < NZ / 2; q += kThreadsQ) {
+  for (int q = tid; q < NY; q += kThreadsH) tw2s[q] = ldg_cpx(p.k2.tw + (q % P2::M) * (q / P2::M));
+  for (int q = tid; q < NZ / 2; q += kThreadsH) {
     twHs[q] = ldg_cpx(p.k3.twH + (q % P3::M) * (q / P3::M));
     twNs[q] = ldg_cpx(p.k3.twN + q);
   }
   __syncthreads();
   char* const gbase = reinterpret_cast<char*>(p.k3.buf);
 
-  if (tid >= kConsumers) {
-    if (tid == kConsumers) {
-      // ===== loader (as k23q; every tile arrives as two half tiles) =====
+  if (tid >= kFftThreadsH) {
+    if (tid == kFftThreadsH) {
+      // ===== loader: one ticket = one half tile =====
       tma_prefetch_desc(&map_in);
       unsigned int ticket = atomicAdd(p.ticket, 1u);
       int b = 0, ph = 0;
       for (int n = 0;; ++n) {
         const unsigned int ticket_next = atomicAdd(p.ticket, 1u);
-        if (n >= 3) mbar_wait(&empty[b], ph ^ 1);
+        if (n >= kSlotsH) mbar_wait(&empty[b], ph ^ 1);   // (ph flips every kSlotsH half tiles)
         int type, plane, idx;
         k23_decode(p, ticket, type, plane, idx);
         ticket = ticket_next;
         desc[4 * b + 0] = type; desc[4 * b + 1] = plane; desc[4 * b + 2] = idx;
-        cpx<float>* dst = buf0 + b * kBufElems;
+        cpx<float>* dst = buf0 + b * kSlotElems;
         if (type == kTileEnd) {
-          mbar_arrive(&full[b]);
+          // every group has to see the end: publish it in this slot and in the next two
+          for (int e = 0; e < kGroupsH; ++e) {
+            if (e > 0) {
+              if (++b == kSlotsH) { b = 0; ph ^= 1; }
+              if (n + e >= kSlotsH) mbar_wait(&empty[b], ph ^ 1);
+              desc[4 * b + 0] = kTileEnd;
+            }
+            mbar_arrive(&full[b]);
+          }
           break;
         }
         if (type == kTileK2) {
-          const int z0 = idx * P2::TZ;
-          mbar_expect_tx(&full[b], (uint32_t)P2::kDenseBytes);
-          for (int g = 0; g < 2; ++g)
-            for (int r0 = 0; r0 < NY; r0 += p.k2.box_rows) {
-              const int src = r0 / p.k2.rows_per_src, rl = r0 - src * p.k2.rows_per_src;
-              tma_load_4d(dst + g * kHalfElems + r0 * TZh, &map_in, &full[b], 2 * (z0 + g * TZh), rl, plane, src);
-            }
+          const int z0 = idx * TZh;
+          mbar_expect_tx(&full[b], (uint32_t)G::kDense2);
+          for (int r0 = 0; r0 < NY; r0 += p.k2.box_rows) {
+            const int src = r0 / p.k2.rows_per_src, rl = r0 - src * p.k2.rows_per_src;
+            tma_load_4d(dst + r0 * TZh, &map_in, &full[b], 2 * z0, rl, plane, src);
+          }
         } else {
           for (;;) {
             unsigned int have;
@@ -317,28 +307,40 @@ k23h_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant_
             __nanosleep(200);
           }
           asm volatile("fence.proxy.async;" ::: "memory");
-          const size_t off = ((size_t)plane * p.t3 + idx) * (size_t)P3::kDenseBytes;
-          mbar_expect_tx(&full[b], (uint32_t)P3::kDenseBytes);
-          for (int g = 0; g < 2; ++g)
-            bulk_g2s(dst + g * kHalfElems, gbase + off + (size_t)g * kHalf3Bytes, kHalf3Bytes, &full[b]);
+          const size_t off = ((size_t)plane * p.t3 + idx) * (size_t)G::kDense3;
+          mbar_expect_tx(&full[b], (uint32_t)G::kDense3);
+          bulk_g2s(dst, gbase + off, (uint32_t)G::kDense3, &full[b]);
         }
-        if (++b == 3) { b = 0; ph ^= 1; }
+        if (++b == kSlotsH) { b = 0; ph ^= 1; }
       }
-    } else if (tid == kConsumers + 32) {
-      // ===== storer (as k23q) =====
+    } else if (tid == kFftThreadsH + 32) {
+      // ===== storer =====
+      // Up to kRd stores may still be reading their slots when the next one is issued: with one
+      // half tile every ~1.3 us per SM, waiting for each read-out in turn (k23q's scheme) makes
+      // this thread's serial chain the bottleneck.  A slot goes back to the loader kRd stores later.
       tma_prefetch_desc(&map_out);
-      constexpr int kSigLag = RF_K23Q_SIGLAG;
+      constexpr int kSigLag = 2 * RF_K23Q_SIGLAG;
+      constexpr int kRd = 2;
       int pend[kSigLag];
+      int rd[kRd];
 #pragma unroll
       for (int q = 0; q < kSigLag; ++q) pend[q] = -1;
+#pragma unroll
+      for (int q = 0; q < kRd; ++q) rd[q] = -1;
       auto signal = [&](int plane) {
         if (plane >= 0) {
           asm volatile("fence.proxy.async;" ::: "memory");
           asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p.plane_done + plane) : "memory");
         }
       };
+      // before sitting idle: hand back every slot and signal every finished plane
       auto flush = [&]() {
         bulk_wait0();
+#pragma unroll
+        for (int q = 0; q < kRd; ++q) {
+          if (rd[q] >= 0) mbar_arrive(&empty[rd[q]]);
+          rd[q] = -1;
+        }
 #pragma unroll
         for (int q = 0; q < kSigLag; ++q) { signal(pend[q]); pend[q] = -1; }
       };
@@ -354,60 +356,57 @@ k23h_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant_
           flush();
           mbar_wait(&done[b], ph);
         }
-        const cpx<float>* src = buf0 + b * kBufElems;
+        const cpx<float>* src = buf0 + b * kSlotElems;
         if (type == kTileK2) {
-          const int z0 = idx * P2::TZ;
-          constexpr int kBox = P2::kBoxRows;
-          for (int g = 0; g < 2; ++g)
-            for (int r0 = 0; r0 < NY; r0 += kBox)
-              tma_store_3d(&map_out, src + g * kHalfElems + r0 * TZh, 2 * (z0 + g * TZh), r0, plane);
+          const int z0 = idx * TZh;
+          for (int r0 = 0; r0 < NY; r0 += P2::kBoxRows) tma_store_3d(&map_out, src + r0 * TZh, 2 * z0, r0, plane);
         } else {
-          const size_t off = ((size_t)plane * p.t3 + idx) * (size_t)P3::kDenseBytes;
-          for (int g = 0; g < 2; ++g)
-            bulk_s2g(gbase + off + (size_t)g * kHalf3Bytes, src + g * kHalfElems, kHalf3Bytes);
+          const size_t off = ((size_t)plane * p.t3 + idx) * (size_t)G::kDense3;
+          bulk_s2g(gbase + off, src, (uint32_t)G::kDense3);
         }
         bulk_commit();
-        bulk_wait_read0();
-        mbar_arrive(&empty[b]);
+        // the store issued kRd half tiles ago has been read out of its slot
+        asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kRd) : "memory");
+        if (rd[0] >= 0) mbar_arrive(&empty[rd[0]]);
+#pragma unroll
+        for (int q = 0; q + 1 < kRd; ++q) rd[q] = rd[q + 1];
+        rd[kRd - 1] = b;
         asm volatile("cp.async.bulk.wait_group %0;" ::"n"(kSigLag) : "memory");
         signal(pend[0]);
 #pragma unroll
         for (int q = 0; q + 1 < kSigLag; ++q) pend[q] = pend[q + 1];
         pend[kSigLag - 1] = type == kTileK2 ? plane : -1;
-        if (++b == 3) { b = 0; ph ^= 1; }
+        if (++b == kSlotsH) { b = 0; ph ^= 1; }
       }
       flush();
     }
     return;
   }
 
-  // ===== FFT warps: two groups of four =====
+  // ===== FFT warps: three groups of four; group g takes half tiles g, g + 3, ... of this CTA =====
   const int grp = tid / kGroupH, t = tid % kGroupH;
   const GroupSync gsync{2 + grp};
-  const FmaToken tok{4 + grp, 4 + (1 - grp)};
-  if (grp == 1) named_arrive(4, kConsumers);      // group 0 holds the token first
   double s1 = 0.0, s2 = 0.0;
   const float* zs = p.k3.zscale;
-  int b = 0, ph = 0;
+  int b = grp, ph = 0;      // slots grp, grp + 3, grp, ...: the phase flips every second visit
   for (;;) {
-    cpx<float>* const B = buf0 + b * kBufElems + grp * kHalfElems;
+    cpx<float>* const B = buf0 + b * kSlotElems;
     mbar_wait(&full[b], ph);
     const int type = desc[4 * b + 0];
     if (type == kTileEnd) break;
     if (type == kTileK2) {
-      k2h_tile_body<NY>(B, t, tw2s, gsync, tok);
+      k2h_tile_body<NY>(B, t, tw2s, gsync);
     } else {
       cpx<float> a1 = {0.f, 0.f}, a2 = {0.f, 0.f};
-      k3h_tile_body<NZ>(B, t, twHs, twNs, zs, a1, a2, gsync, tok);
+      k3h_tile_body<NZ>(B, t, twHs, twNs, zs, a1, a2, gsync);
       s1 += (double)a1.x + (double)a1.y;
       s2 += (double)a2.x + (double)a2.y;
     }
     fence_proxy_async();
     mbar_arrive(&done[b]);
-    if (++b == 3) { b = 0; ph ^= 1; }
+    b += kGroupsH;
+    if (b >= kSlotsH) { b -= kSlotsH; ph ^= 1; }
   }
-  // the last release of group 1 has no taker: consume it so that no barrier is left half-arrived
-  if (grp == 0) named_sync(4, kConsumers);
 
   if (p.k3.partials) {
 #pragma unroll
@@ -415,13 +414,13 @@ k23h_fused_yz(const __grid_constant__ CUtensorMap map_in, const __grid_constant_
       s1 += __shfl_xor_sync(0xffffffffu, s1, o);
       s2 += __shfl_xor_sync(0xffffffffu, s2, o);
     }
-    __shared__ double red[2][kConsumers / 32];
+    __shared__ double red[2][kFftThreadsH / 32];
     const int wid = tid >> 5, lane = tid & 31;
     if (lane == 0) { red[0][wid] = s1; red[1][wid] = s2; }
-    ConsumerSync()();
+    named_sync(1, kFftThreadsH);
     if (tid == 0) {
       double t1 = 0, t2 = 0;
-      for (int q = 0; q < kConsumers / 32; ++q) { t1 += red[0][q]; t2 += red[1][q]; }
+      for (int q = 0; q < kFftThreadsH / 32; ++q) { t1 += red[0][q]; t2 += red[1][q]; }
       p.k3.partials[2 * (size_t)blockIdx.x] = t1;
       p.k3.partials[2 * (size_t)blockIdx.x + 1] = t2;
     }
