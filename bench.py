@@ -470,6 +470,12 @@ def run_ours(args):
             tj = json.load(f)
         if tj.get("grid") == list(grid) and world == 1:
             traffic = tj["dram_bytes_per_launch"].get(names[dom])
+        elif names[dom] in tj.get("dram_bytes_per_cell", {}):
+            # 2048 / 4096-point kernels: DRAM bytes per cell from the ncu capture of the same kernel
+            # instantiation on a smaller grid, times the cells one launch of this run processes
+            per_cell = tj["dram_bytes_per_cell"][names[dom]].get(str(grid[0] if dom == 0 else grid[1]))
+            if per_cell:
+                traffic = per_cell * local_cells     # (chunked runs: summed over the pass's launches, like kernels_ms)
     except Exception:
         pass
     issue = None

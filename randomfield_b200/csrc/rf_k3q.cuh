@@ -51,6 +51,19 @@ __device__ __forceinline__ void k3q_load_twiddles(cpx<float> (&twr)[LPlan<NZ>::R
       twr2[k1] = ld(tabH + (TRANSPOSED ? k1 * M + j1 : P::SPLIT * j1 * k1));
     });
     twu[0] = ld(tabN + (pp == 0 ? M / 2 : pp));
+  } else if constexpr (P::SPLIT == 2 && (H / 4) % kConsumers == 0) {
+    // quad sweep: twu[2q] = W_NZ^k, twu[2q+1] = W_NZ^(H/2-k), k = tid + 256 q < H/4
+    sfor<0, K3Consts<NZ>::kPairsPerThread / 2>([&](auto qi) {
+      constexpr int q = decltype(qi)::value;
+      const int k = tid + q * kConsumers;
+      twu[2 * q] = ld(tabN + k);
+      twu[2 * q + 1] = ld(tabN + (H / 2 - k) % (H / 2) + (k == 0 ? H / 4 : 0));   // k = 0: the (H/4, 3H/4) pair
+    });
+    sfor<0, R1>([&](auto ki) {
+      constexpr int k1 = decltype(ki)::value;
+      twr[k1] = ld(tabH + (TRANSPOSED ? k1 * M + tid % M : P::SPLIT * (tid % M) * k1));
+      twr2[k1] = twr[k1];
+    });
   } else {
     sfor<0, K3Consts<NZ>::kPairsPerThread>([&](auto qi) {
       constexpr int q = decltype(qi)::value;
@@ -149,6 +162,42 @@ __device__ __forceinline__ void k3q_tile_body(cpx<float>* __restrict__ B, int ti
     });
     ConsumerSync()();
   } else {
+  if constexpr (P::SPLIT == 2 && (H / 4) % kConsumers == 0) {
+    // ---- Hermitian unpack AND the radix-2 split across the line halves in ONE sweep ----
+    // The unpack pairs (k, H-k), (H/2-k, H/2+k) and the split butterflies (k, k+H/2), (H/2-k, H-k) close
+    // over the four elements {k, H/2-k, H/2+k, H-k}: one read and one write of the tile instead of two
+    // of each, one barrier instead of two.  Same operations on the same values as the two sweeps.
+    constexpr int QPT = (H / 4) / kConsumers;     // quads per thread and line
+    static_assert(2 * QPT == kPairsPerThread, "twiddle registers");
+#pragma unroll 1
+    for (int l = 0; l < P::TL; ++l) {
+      cpx<float>* Lp = B + l * H;
+      sfor<0, QPT>([&](auto qi) {
+        constexpr int q = decltype(qi)::value;
+        const int k = tid + q * kConsumers;       // 0 <= k < H/4
+        if (q == 0 && k == 0) {
+          // k = 0: the real ends (0, H/2) and their butterfly (W^0 = 1); and the self-paired (H/4, 3H/4)
+          cpx<float> z0, zm;
+          c2r_unpack_ends(Lp[0], Lp[H / 2], z0, zm);
+          Lp[0] = z0 + zm;
+          Lp[H / 2] = cmul(z0 - zm, ldg_cpx(twH));
+          cpx<float> za, zb;
+          c2r_unpack_pair(Lp[H / 4], Lp[3 * H / 4], twu[2 * q + 1], za, zb);   // twN[H/4 - 0 ... ] see loader
+          Lp[H / 4] = za + zb;
+          Lp[3 * H / 4] = cmul(za - zb, ldg_cpx(twH + H / 4));
+        } else {
+          cpx<float> z1, z4, z2, z3;
+          c2r_unpack_pair(Lp[k], Lp[H - k], twu[2 * q], z1, z4);                       // Z[k], Z[H-k]
+          c2r_unpack_pair(Lp[H / 2 - k], Lp[H / 2 + k], twu[2 * q + 1], z2, z3);       // Z[H/2-k], Z[H/2+k]
+          Lp[k] = z1 + z3;
+          Lp[H / 2 + k] = cmul(z1 - z3, ldg_cpx(twH + k));
+          Lp[H / 2 - k] = z2 + z4;
+          Lp[H - k] = cmul(z2 - z4, ldg_cpx(twH + H / 2 - k));
+        }
+      });
+    }
+    ConsumerSync()();
+  } else {
   // ---- Hermitian unpack, in place (as k3_tile_body) ----
   if constexpr (H / 2 >= kConsumers) {
 #pragma unroll 2
@@ -192,6 +241,7 @@ __device__ __forceinline__ void k3q_tile_body(cpx<float>* __restrict__ B, int ti
     }
     ConsumerSync()();
   }
+  }   // (separate unpack / split sweeps)
   // ---- step A: dense -> registers | barrier | registers -> padded ----
   cpx<float> v[IA][R1];
   sfor<0, IA>([&](auto qi) {

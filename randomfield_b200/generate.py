@@ -342,6 +342,7 @@ class Generator(object):
 
         Returns a float32 (or float64) array of shape (nx, ny, nz): a view of this
         generator's host buffer that later calls overwrite."""
+        self._check_plot(show_plot, save_plot_name)
         if seed is None:
             seed = int.from_bytes(os.urandom(8), 'little')
             if self._slab is not None:      # every rank must draw the same field
@@ -378,6 +379,7 @@ class Generator(object):
                                  show_plot=False, save_plot_name=None):
         """Convert the delta field into a light-cone density field in g/cm**3
         (generate.py:232-280), in place on the device."""
+        self._check_plot(show_plot, save_plot_name)
         if self._field_kind is None:
             raise RuntimeError('No delta field in the buffer.')
         self._engine.density(apply_lognormal_transform, float(self.delta_field_rms),
@@ -393,6 +395,7 @@ class Generator(object):
                                       show_plot=False, save_plot_name=None):
         """Newtonian potential Phi(r) in s**-2 (generate.py:282-350): inverse transform of
         -(3/2) H0^2 Om0 delta(k)/k^2, times G(z)/(1+z) on the light cone."""
+        self._check_plot(show_plot, save_plot_name)
         if self._potential_args is None:
             raise RuntimeError('No saved potential field.')
         seed, smoothing = self._potential_args
@@ -417,6 +420,7 @@ class Generator(object):
         calculate_newtonian_potential first) into a separate array, as the reference does
         (generate.py:398-399): the potential and the host array returned for it stay intact, and
         the call can be repeated with another i_min."""
+        self._check_plot(show_plot, save_plot_name)
         nDC = self.DC.size
         if i_min is None:
             i_min = nDC // 32
@@ -435,10 +439,14 @@ class Generator(object):
                             label='Lensing potential $\\psi(r)$ [(Mpc/h) s$^{-2}$]')
         return field
 
+    @staticmethod
+    def _check_plot(show_plot, save_plot_name):
+        """Plotting (generate.py:420-516, matplotlib on a host copy) is outside the B200 path: a
+        request for it fails BEFORE any field is generated, not after."""
+        if show_plot or save_plot_name is not None:
+            raise NotImplementedError('plot_slice is outside the B200 field-synthesis path: plot the returned '
+                                      'array with the reference\'s plot_slice or matplotlib directly.')
+
     def plot_slice(self, *args, **kwargs):
-        """generate.py:420-516 needs matplotlib, which is not installed on the GPU box."""
-        try:
-            import matplotlib  # noqa: F401
-        except ImportError:
-            raise ImportError('plot_slice requires matplotlib.')
-        raise NotImplementedError('plot_slice is outside the B200 field-synthesis path.')
+        """generate.py:420-516: matplotlib slice plots of a host array -- not part of this path."""
+        self._check_plot(True, None)

@@ -456,6 +456,18 @@ def test_newtonian_potential_needs_saved_potential(rf):
         gen.calculate_newtonian_potential()
 
 
+def test_plot_requests_fail_before_any_work(rf):
+    """plot_slice is outside the path: show_plot / save_plot_name raise before a field is generated."""
+    gen = rf.Generator(64, 64, 64, 2.0)
+    with pytest.raises(NotImplementedError):
+        gen.generate_delta_field(seed=1, show_plot=True)
+    assert gen._last is None
+    gen.generate_delta_field(seed=1)
+    with pytest.raises(NotImplementedError):
+        gen.convert_delta_to_density(save_plot_name='x.png')
+    assert gen._field_kind == 'delta'
+
+
 def test_potential_attribute_has_no_side_effect(rf):
     """reading generator.potential / plan_c2r.data_in must not destroy the delta field."""
     gen = rf.Generator(64, 64, 64, 2.0)
