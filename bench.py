@@ -149,6 +149,18 @@ def run_reference(args):
     total = float(np.sum(times))
     value = args.steps * n ** 3 / total / 1e6
     sample = cpu_sample_text(n, grid, kind)
+    # one untimed-for-the-metric step at the FULL grid of the single-GPU workload (the reference needs
+    # 16 B per mode of temporaries: 16 GB at 1024^3), reported next to the sampled value
+    full = None
+    if args.gpus == 1 and grid[0] == grid[1] == grid[2] and grid[0] > n and not args.quick:
+        try:
+            import psutil
+            if psutil.virtual_memory().available > 6 * 4 * float(grid[0]) ** 3:
+                sec, _ = cpu_reference_step(grid[0], 123)
+                full = {"grid": list(grid), "seconds": sec, "Mcells_s": float(grid[0]) ** 3 / sec / 1e6,
+                        "note": "one step at the full grid, same code path as the sampled steps"}
+        except Exception as exc:      # MemoryError etc.: the sampled value stands
+            full = {"grid": list(grid), "error": repr(exc)[:200]}
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
@@ -156,7 +168,7 @@ def run_reference(args):
         "data": "synthetic", "config": workload_config(grid, args.gpus),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
+        "gpu_launches": 0, "full_grid_step": full,
     }
     print(json.dumps(line))
     return 0
@@ -199,7 +211,9 @@ def workload_config(grid, world, mode=None):
                    "of z columns",
         "nccl": "NCCL all-to-all"}.get(mode, mode)
     return {"workload": workload_name(grid, world), "grid": list(grid),
-            "l2": "working set %.1f GB per GPU >> 126 MB L2, no flush needed" % (4 * local / 1e9),
+            "l2": ("working set %.1f GB per GPU >> 126 MB L2, no flush needed" % (4 * local / 1e9)) if 4 * local > 1e9
+            else ("working set %.2f GB per GPU is not >> the 126 MB L2 and L2 is not flushed: not a contract configuration"
+                  % (4 * local / 1e9)),
             "parallelism": par}
 
 
