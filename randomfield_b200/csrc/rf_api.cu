@@ -1743,6 +1743,119 @@ __global__ void pk_bin_kernel(const cpx<T>* f, int nx, int ny, int nz, double k0
   }
 }
 
+// |G|^2 of the packed-Nyquist layout [nx][ny][nz/2] the fast forward transform leaves (rf_k3f.cuh): column
+// 0 holds C = F0 + i FN, the transforms of the two real planes iz = 0 and iz = nz/2, which come apart
+// as F0[k] = (C[k] + conj C[-k]) / 2, FN[k] = (C[k] - conj C[-k]) / 2i with -k = (-ix, -iy).
+__global__ void pk_bin_packed_kernel(const cpx<float>* f, int nx, int ny, int nz, double k0x, double k0y, double k0z,
+                                     int nbins, const double* __restrict__ edges, double* __restrict__ sums,
+                                     unsigned long long* __restrict__ counts) {
+  extern __shared__ __align__(16) unsigned char pk_smem[];
+  double* ss = reinterpret_cast<double*>(pk_smem);
+  unsigned long long* sc = reinterpret_cast<unsigned long long*>(ss + nbins);
+  for (int b = threadIdx.x; b < nbins; b += blockDim.x) { ss[b] = 0.0; sc[b] = 0ull; }
+  __syncthreads();
+  const int nzc = nz / 2;
+  const long long total = (long long)nx * ny * nzc;
+  auto add = [&](double k, double p, int w) {
+    if (!(k >= edges[0]) || k >= edges[nbins]) return;
+    int lo = 0, hi = nbins;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (edges[mid] <= k) lo = mid; else hi = mid;
+    }
+    atomicAdd(&ss[lo], w * p);
+    atomicAdd(&sc[lo], (unsigned long long)w);
+  };
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int iz = (int)(i % nzc);
+    const long long r = i / nzc;
+    const int iy = (int)(r % ny), ix = (int)(r / ny);
+    const double jx = ix <= nx / 2 ? ix : ix - nx, jy = iy <= ny / 2 ? iy : iy - ny;
+    const double kxy2 = jx * jx * k0x * k0x + jy * jy * k0y * k0y;
+    const cpx<float> v = f[i];
+    if (iz > 0) {
+      add(sqrt(kxy2 + (double)iz * iz * k0z * k0z), (double)v.x * v.x + (double)v.y * v.y, 2);
+    } else {
+      const cpx<float> m = f[((long long)((nx - ix) % nx) * ny + (ny - iy) % ny) * nzc];
+      const double ar = 0.5 * ((double)v.x + m.x), ai = 0.5 * ((double)v.y - m.y);     // F0
+      const double br = 0.5 * ((double)v.y + m.y), bi = -0.5 * ((double)v.x - m.x);    // FN
+      add(sqrt(kxy2), ar * ar + ai * ai, 1);
+      add(sqrt(kxy2 + (double)nzc * nzc * k0z * k0z), br * br + bi * bi, 1);
+    }
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < nbins; b += blockDim.x) {
+    if (sc[b]) {
+      atomicAdd(&sums[b], ss[b]);
+      atomicAdd(&counts[b], sc[b]);
+    }
+  }
+}
+
+// in-place inverse-sign FFT along a strided axis of a packed [..][..][nzc] complex buffer on the pipelined
+// y-pass kernels: lines of n points `row_stride` elements apart, `nouter` of them `outer_stride` apart
+static int pipe_strided_pass(rf_ctx* c, void* buf, int n, const void* tw, long long row_stride, int nouter,
+                             long long outer_stride) {
+  const int nzc = c->nz / 2;
+  pipe::K2PParams q;
+  q.tw = (const cpx<float>*)tw;
+  q.rows_per_src = n;
+  q.out = (cpx<float>*)buf; q.out_outer = outer_stride; q.out_row = row_stride;
+  q.z_out_base = 0;
+  CUtensorMap min, mout;
+  int e = 0;
+  RF_DISPATCH_PIPE(n, {
+    const int tz = PipeLaunch<NN>::tile_cols();
+    if (nzc % tz) return fail(RF_ERR_ARG, "strided pass: nz/2 is not a multiple of the tile width");
+    q.ztiles = nzc / tz;
+    q.tile0 = 0;
+    q.ntiles = nouter * q.ztiles;
+    q.box_rows = std::min(PipeLaunch<NN>::box_rows(), n);
+    uint64_t din[4] = {(uint64_t)2 * nzc, (uint64_t)n, (uint64_t)nouter, 1};
+    uint64_t sin[3] = {(uint64_t)row_stride * 8, (uint64_t)outer_stride * 8, (uint64_t)row_stride * 8 * n};
+    uint32_t bin[4] = {(uint32_t)2 * tz, (uint32_t)q.box_rows, 1, 1};
+    int e2 = make_tensor_map(&min, buf, 4, din, sin, bin);
+    if (e2) return e2;
+    uint64_t dout[3] = {(uint64_t)2 * nzc, (uint64_t)n, (uint64_t)nouter};
+    uint64_t sout[2] = {(uint64_t)row_stride * 8, (uint64_t)outer_stride * 8};
+    uint32_t bout[3] = {(uint32_t)2 * tz, (uint32_t)PipeLaunch<NN>::box_rows(), 1};
+    e2 = make_tensor_map(&mout, buf, 3, dout, sout, bout);
+    if (e2) return e2;
+    const int grid = std::min(q.ntiles, PipeLaunch<NN>::ctas_per_sm() * c->num_sms);
+    e = PipeLaunch<NN>::k2p(min, mout, q, grid, c->stream);
+  });
+  c->launches++;
+  RF_CUDA(e);
+  return RF_OK;
+}
+
+// forward transform on the fast kernels: real field -> copy in the auxiliary buffer -> r2c along z (k3f),
+// then the inverse-sign y and x passes (|F| = |conj F|); returns with the packed spectrum in c->recv
+static int r2c_fast(rf_ctx* c) {
+  const size_t bytes = (size_t)c->nx * c->ny * c->nz * sizeof(float);
+  RF_CUDA(cudaMemcpyAsync(c->recv, c->field, bytes, cudaMemcpyDeviceToDevice, c->stream));
+  c->launches++;
+  pipe::K3PParams q;
+  q.buf = (float*)c->recv;
+  q.twH = (const cpx<float>*)c->tw_zh;
+  q.twN = (const cpx<float>*)c->tw_z;
+  q.zscale = nullptr;
+  q.partials = nullptr;
+  q.tile0 = 0;
+  int e = 0;
+  RF_DISPATCH_PIPE(c->nz, {
+    q.ntiles = (int)((long long)c->nx * c->ny / PipeLaunch<NN>::k3p_lines_per_tile());
+    e = PipeLaunch<NN>::k3f(q, std::min(q.ntiles, c->num_sms), c->stream);
+  });
+  c->launches++;
+  RF_CUDA(e);
+  const long long nzc = c->nz / 2;
+  e = pipe_strided_pass(c, c->recv, c->ny, c->tw_y, nzc, c->nx, (long long)c->ny * nzc);   // y
+  if (e) return e;
+  return pipe_strided_pass(c, c->recv, c->nx, c->tw_x, (long long)c->ny * nzc, c->ny, nzc);   // x
+}
+
 template <typename T>
 static int r2c_power_impl(rf_ctx* c, int nbins, const double* edges, double* out_pk, long long* out_counts) {
   const int nx = c->nx, ny = c->ny, nz = c->nz, nzh = nz / 2 + 1;
@@ -1750,13 +1863,25 @@ static int r2c_power_impl(rf_ctx* c, int nbins, const double* edges, double* out
   // the real field stays as it is
   if (!c->recv) RF_CUDA(cudaMalloc(&c->recv, c->buf_bytes));
   c->aux_is_psi = false;
-  const long long plane = (long long)ny * nzh;
-  int e = run_generic_axis<T>(c, c->field, c->recv, 2, 0, nz, (long long)nx * ny, 1, nz, 0, nzh, 0, 1, 1, (T)1, c->stream);
-  if (e) return e;
-  e = run_generic_axis<T>(c, c->recv, c->recv, 0, 0, ny, nx, nzh, plane, 1, plane, 1, nzh, nzh, (T)1, c->stream);
-  if (e) return e;
-  e = run_generic_axis<T>(c, c->recv, c->recv, 0, 0, nx, ny, nzh, nzh, 1, nzh, 1, plane, plane, (T)1, c->stream);
-  if (e) return e;
+  // float32 grids of the tile kernels (every axis a power of two in [64, 4096], nz >= 128): the pipelined
+  // kernels of the hot path, run in the forward direction; everything else: any-length line transforms
+  bool fast = false;
+  if constexpr (std::is_same<T, float>::value)
+    fast = c->pipe && c->nz >= 128 && (c->ny <= 1024 || c->big) && (c->nx <= 1024 || c->big) &&
+           (long long)c->nx * c->ny % 256 == 0;
+  int e = 0;
+  if (fast) {
+    e = r2c_fast(c);
+    if (e) return e;
+  } else {
+    const long long plane = (long long)ny * nzh;
+    e = run_generic_axis<T>(c, c->field, c->recv, 2, 0, nz, (long long)nx * ny, 1, nz, 0, nzh, 0, 1, 1, (T)1, c->stream);
+    if (e) return e;
+    e = run_generic_axis<T>(c, c->recv, c->recv, 0, 0, ny, nx, nzh, plane, 1, plane, 1, nzh, nzh, (T)1, c->stream);
+    if (e) return e;
+    e = run_generic_axis<T>(c, c->recv, c->recv, 0, 0, nx, ny, nzh, nzh, 1, nzh, 1, plane, plane, (T)1, c->stream);
+    if (e) return e;
+  }
   double* dev = nullptr;
   const size_t bytes = sizeof(double) * (nbins + 1) + sizeof(double) * nbins + sizeof(unsigned long long) * nbins;
   RF_CUDA(cudaMalloc((void**)&dev, bytes));
@@ -1769,7 +1894,12 @@ static int r2c_power_impl(rf_ctx* c, int nbins, const double* edges, double* out
   const long long total = (long long)nx * ny * nzh;
   const int grid = (int)std::min<long long>((total + 255) / 256, (long long)c->num_sms * 8);
   if (ce == cudaSuccess) {
-    pk_bin_kernel<T><<<grid, 256, nbins * 16, c->stream>>>((const cpx<T>*)c->recv, nx, ny, nz, two_pi / (nx * c->spacing),
+    if (fast)
+      pk_bin_packed_kernel<<<grid, 256, nbins * 16, c->stream>>>((const cpx<float>*)c->recv, nx, ny, nz,
+                                                                 two_pi / (nx * c->spacing), two_pi / (ny * c->spacing),
+                                                                 two_pi / (nz * c->spacing), nbins, d_edges, d_sums, d_counts);
+    else
+      pk_bin_kernel<T><<<grid, 256, nbins * 16, c->stream>>>((const cpx<T>*)c->recv, nx, ny, nz, two_pi / (nx * c->spacing),
                                                           two_pi / (ny * c->spacing), two_pi / (nz * c->spacing), nbins,
                                                           d_edges, d_sums, d_counts);
     c->launches++;

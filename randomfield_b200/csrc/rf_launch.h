@@ -7,6 +7,7 @@
 #include "rf_big.cuh"
 #include "rf_k3q.cuh"
 #include "rf_k23q.cuh"
+#include "rf_k3f.cuh"
 
 namespace rf {
 
@@ -25,6 +26,8 @@ struct PipeLaunch {
   static int k3p(const pipe::K3PParams& p, int grid, cudaStream_t s);
   static int k3p_lines_per_tile();
   static int k3q(const pipe::K3PParams& p, int grid, cudaStream_t s);   // three-deep ring, in-place tiles
+  // forward direction of the same axis: r2c lines (inverse sign; rf_k3f.cuh), N >= 128
+  static int k3f(const pipe::K3PParams& p, int grid, cudaStream_t s);
   // N <= 1024: rf_pipe.cuh kernels; N = 2048, 4096: the single-buffer kernels of rf_big.cuh
   static int k2p(const CUtensorMap& in, const CUtensorMap& out, const pipe::K2PParams& p, int grid,
                  cudaStream_t s);

@@ -36,6 +36,18 @@ int PipeLaunch<N>::k3q(const pipe::K3PParams& p, int grid, cudaStream_t s) {
   }
 }
 template <>
+int PipeLaunch<N>::k3f(const pipe::K3PParams& p, int grid, cudaStream_t s) {
+  constexpr int smem = pipe::k3q_smem_bytes<N>();
+  if constexpr (smem <= 227 * 1024) {
+    int e;
+    if ((e = set_smem_pipe(pipe::k3f_r2c_lines<N>, smem))) return e;
+    pipe::k3f_r2c_lines<N><<<grid, pipe::kThreads, smem, s>>>(p);
+    return (int)cudaGetLastError();
+  } else {
+    return (int)cudaErrorInvalidConfiguration;   // nz = 64: the estimator uses the generic line transform
+  }
+}
+template <>
 int PipeLaunch<N>::k3p_lines_per_tile() {
   return pipe::LPlan<N>::TL;
 }

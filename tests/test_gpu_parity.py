@@ -230,6 +230,9 @@ def _numpy_shell_power(delta, spacing, edges):
 
 
 @pytest.mark.parametrize("shape,dtype", [((128, 128, 128), np.float32), ((64, 128, 256), np.float32),
+                                         ((256, 256, 256), np.float32), ((64, 2048, 128), np.float32),
+                                         ((1024, 64, 512), np.float32),          # fast forward kernels (k3f + k2p / k2b)
+                                         ((64, 64, 64), np.float32),             # nz = 64: generic line transforms
                                          ((32, 48, 40), np.float32), ((64, 64, 64), np.float64)])
 def test_power_spectrum_recovered(lib, shape, dtype):
     """Gate 4: the measured P(k) of the generated field -- forward r2c transform and shell binning
@@ -243,7 +246,9 @@ def test_power_spectrum_recovered(lib, shape, dtype):
     eng.generate_delta(seed)
     delta = eng.copy_field()
     kmin = 2 * np.pi / (spacing * min(shape))
-    edges = np.linspace(1.5 * kmin, np.pi / spacing, 21)
+    # (the first shells hold a handful of modes each: they compare single modes of the two transforms)
+    # (edges at irrational multiples of the lattice spacing: no mode sits on an edge)
+    edges = np.concatenate([[0.5031 * kmin, 1.2073 * kmin], np.linspace(1.5119 * kmin, 0.99937 * np.pi / spacing, 21)])
     pk, cnt = eng.r2c_power(edges)
     assert np.array_equal(eng.copy_field(), delta)          # the estimator leaves the field alone
     pk_np, cnt_np = _numpy_shell_power(delta, spacing, edges)
@@ -260,7 +265,7 @@ def test_power_spectrum_recovered(lib, shape, dtype):
     ok = (which >= 0) & (which < len(edges) - 1)
     want = np.bincount(which[ok], weights=(w * pk_in)[ok], minlength=len(edges) - 1) / np.maximum(cnt_np, 1)
     good = cnt > 100
-    assert good.sum() >= 15
+    assert good.sum() >= 12
     dev = (pk[good] / want[good] - 1.0) * np.sqrt(cnt[good] / 2.0)
     assert np.abs(dev).max() < 5.0, dev
     assert abs(dev.mean()) < 5.0 / np.sqrt(good.sum())
