@@ -24,6 +24,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.environ.get("RF_REFERENCE_ROOT", "/root/reference")
 DST = os.path.join(HERE, "_ref")
 FILES = ["randomfield/transform.py", "randomfield/powertools.py", "randomfield/random.py",
+         "randomfield/generate.py",          # only for the lensing loop (ref_replay.lensing_replay)
          "randomfield/data/default_power.dat"]
 
 

@@ -484,10 +484,14 @@ def philox_kfield_big(shape, spacing, power, seed, smoothing=0.0, potential=Fals
 
 
 # ------------------------------------------------------------------------------------------
-# part 3: lensing potential.  Parity status: UNPINNED -- the
-# reference's calculate_lensing_potential cannot run here (astropy absent; scipy 1.18 has no
-# integrate.simps), so this is a restatement of generate.py:374-410 on top of a restatement of
-# the third-party rule it calls.
+# part 3: lensing potential.  Parity status: the LOOP is pinned --
+# oracle/ref_replay.py: lensing_replay runs the reference's calculate_lensing_potential
+# (generate.py:353-418) unmodified on stub attributes, and tests/test_oracle.py compares this
+# restatement with it and with the golden fixture made from it (tests/golden/ref_lensing.npz).
+# What stays a restatement is the third-party rule the loop calls: scipy.integrate.simps
+# (un-vendored, unpinned; removed from scipy 1.14, absent here) -- simps_old below restates the
+# algorithm scipy shipped up to 1.5 (even='avg') and is checked against scipy.integrate.simpson
+# for odd sample counts and against the definition of the 'avg' rule for even ones.
 # ------------------------------------------------------------------------------------------
 def _basic_simps(y, start, stop, x):
     """Composite Simpson over the panels starting at start, start+2, ..., < stop on non-uniform

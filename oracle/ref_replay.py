@@ -127,3 +127,80 @@ def replay(nx, ny, nz, spacing, seed=None, smoothing=0.0, power=None, dtype=np.c
 
 def default_power():
     return modules()[1].load_default_power()
+
+
+# ------------------------------------------------------------------------------------------
+# calculate_lensing_potential (generate.py:353-418) -- the reference's own loop on stubs
+# ------------------------------------------------------------------------------------------
+def _generate_module():
+    """Import the reference's generate.py unmodified.  It cannot be imported as it stands here:
+    astropy is absent (generate.py:13-14, and cosmotools.py needs astropy.cosmology) and scipy >=
+    1.14 has no integrate.simps (generate.py:408).  Stubs for exactly those names are installed
+    first: astropy.units / astropy.constants with the one quantity the method reads (the speed of
+    light in km/s), an empty `cosmotools`, and scipy.integrate.simps = oracle.simps_old, the
+    restatement of the rule scipy shipped when the reference was written.  Only stage the copy
+    when generate.py is there (oracle/make_ref.py copies the three modules of the hot path; this
+    needs the reference tree itself)."""
+    if "generate" in _mods:
+        return _mods["generate"]
+    import types
+    import warnings
+    import scipy.integrate
+    path = os.path.join(_PKG, "generate.py")
+    if not os.path.exists(path):
+        raise RuntimeError("generate.py not found under %s" % _PKG)
+    modules()
+    import oracle
+
+    class _Quantity(object):
+        def __init__(self, value):
+            self.value = value
+
+        def to(self, unit):
+            return self
+
+    units = types.ModuleType("astropy.units")
+
+    class _Unit(object):
+        def __truediv__(self, other):
+            return self
+        __div__ = __truediv__
+    units.km = units.s = units.Mpc = _Unit()
+    constants = types.ModuleType("astropy.constants")
+    constants.c = _Quantity(299792.458)          # km/s, what astropy.constants.c.to(u.km / u.s).value gives
+    astropy = types.ModuleType("astropy")
+    astropy.units, astropy.constants = units, constants
+    saved = {k: sys.modules.get(k) for k in ("astropy", "astropy.units", "astropy.constants", "cosmotools")}
+    sys.modules.update({"astropy": astropy, "astropy.units": units, "astropy.constants": constants,
+                        "cosmotools": types.ModuleType("cosmotools")})
+    if not hasattr(scipy.integrate, "simps"):
+        def simps(y, x=None, dx=1, axis=-1, even='avg'):
+            assert axis == -1 and even == 'avg' and x is not None
+            return oracle.simps_old(y, x)
+        scipy.integrate.simps = simps
+    try:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")          # invalid escape sequences in the docstrings
+            mod = _load("rf_ref_generate", "generate.py", as_name="rf_ref_generate")
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+    _mods["generate"] = mod
+    return mod
+
+
+def generate_available() -> bool:
+    return os.path.exists(os.path.join(_PKG, "generate.py"))
+
+
+def lensing_replay(dphi, DC, DA, Ok0=0.0, i_min=None):
+    """Generator.calculate_lensing_potential (generate.py:353-418) run UNMODIFIED on a stub object
+    that carries the five attributes the method reads."""
+    import types
+    gen = _generate_module()
+    stub = types.SimpleNamespace(DC=np.asarray(DC), DA=np.asarray(DA), cosmology=types.SimpleNamespace(Ok0=Ok0),
+                                 plan_c2r=types.SimpleNamespace(data_out=dphi))
+    return gen.Generator.calculate_lensing_potential(stub, i_min=i_min)

@@ -49,6 +49,20 @@ def main():
             key = "%s_%s" % ("packed" if packed else "full", np.dtype(dt).name)
             out[key + "_in"], out[key + "_out"] = a, b
     np.savez(os.path.join(HERE, "ref_symmetrize.npz"), **out)
+    # calculate_lensing_potential (generate.py:353-418): the reference's own loop, unmodified, on stub
+    # attributes (oracle/ref_replay.py: lensing_replay); scipy.integrate.simps is the restated rule
+    out = {}
+    rng = np.random.RandomState(17)
+    for name, shp, imin, ok0, dt in (("flat_f32", (5, 4, 48), None, 0.0, np.float32), ("open_f32", (4, 3, 33), 3, 0.02, np.float32),
+                                     ("closed_f64", (3, 4, 40), 0, -0.015, np.float64), ("odd_f64", (2, 3, 17), 1, 0.0, np.float64)):
+        nz = shp[2]
+        dphi = (1e-33 * rng.normal(size=shp)).astype(dt)
+        DC = np.arange(nz) * 2.5
+        DA = DC * (1 + 0.002 * np.arange(nz))
+        psi = ref_replay.lensing_replay(dphi, DC, DA, Ok0=ok0, i_min=imin)
+        out[name + "_dphi"], out[name + "_DC"], out[name + "_DA"], out[name + "_psi"] = dphi, DC, DA, psi
+        out[name + "_par"] = np.array([-1 if imin is None else imin, ok0])
+    np.savez(os.path.join(HERE, "ref_lensing.npz"), **out)
     # first deviates of RandomState(123)
     np.savez(os.path.join(HERE, "ref_misc.npz"),
              normal123=np.random.RandomState(123).normal(size=8))

@@ -126,3 +126,37 @@ def test_philox_field_statistics():
     full = np.fft.ifftn(np.concatenate([kf, np.conj(np.roll(np.roll(kf[:, :, 1:-1][:, :, ::-1][::-1, ::-1], 1, 0), 1, 1))], axis=2))
     assert np.abs(full.imag).max() < 1e-9 * np.abs(full.real).max()
     assert bins.min() >= -1 and bins.max() < len(power)
+
+
+LENS_CASES = ["flat_f32", "open_f32", "closed_f64", "odd_f64"]
+
+
+@pytest.mark.parametrize("name", LENS_CASES)
+def test_lensing_oracle_matches_golden(golden_dir, name):
+    """oracle.lensing_potential against psi computed by the reference's OWN loop (generate.py:353-418
+    run unmodified on stub attributes, tests/golden/make_golden.py).  The reference stores its
+    integrand in dPhi's dtype before integrating, the oracle evaluates it in float64: equal to
+    float32 rounding for float32 fields, to 1e-13 for float64 ones."""
+    g = np.load(os.path.join(golden_dir, "ref_lensing.npz"))
+    imin, ok0 = g[name + "_par"]
+    psi = oracle.lensing_potential(g[name + "_dphi"], g[name + "_DC"], g[name + "_DA"], Ok0=float(ok0),
+                                   i_min=None if imin < 0 else int(imin))
+    ref = g[name + "_psi"]
+    assert psi.dtype == ref.dtype and psi.shape == ref.shape
+    scale = np.abs(ref.astype(np.float64)).max()
+    tol = 3e-7 if ref.dtype == np.float32 else 1e-13
+    assert np.abs(psi.astype(np.float64) - ref).max() <= tol * scale
+
+
+@pytest.mark.skipif(not ref_replay.generate_available(), reason="reference tree not mounted")
+def test_lensing_oracle_matches_reference_loop():
+    rng = np.random.RandomState(3)
+    for nz, imin, ok0 in ((64, None, 0.0), (33, 3, 0.0), (40, 0, 0.01), (17, 1, -0.02), (8, 7, 0.0)):
+        dphi = (1e-33 * rng.normal(size=(3, 4, nz))).astype(np.float32)
+        DC = np.arange(nz) * 2.0
+        DA = DC * (1 + 0.001 * np.arange(nz))
+        ref = ref_replay.lensing_replay(dphi, DC, DA, Ok0=ok0, i_min=imin)
+        got = oracle.lensing_potential(dphi, DC, DA, Ok0=ok0, i_min=imin)
+        assert np.abs(got.astype(np.float64) - ref).max() <= 3e-7 * np.abs(ref).max()
+    with pytest.raises(ValueError):
+        ref_replay.lensing_replay(dphi, DC, DA, i_min=nz)
