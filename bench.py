@@ -519,6 +519,9 @@ def run_ours(args):
         "roofline": {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "peak_source": peak_src,
+                     # the same kernel by its DRAM traffic (ncu): what HBM actually carries per launch
+                     "dram_achieved": (traffic / (pass_ms[dom] * 1e-3) / 1e9) if traffic else None,
+                     "dram_frac": (traffic / (pass_ms[dom] * 1e-3) / 1e9 / peak) if traffic else None,
                      "algorithmic_bytes_per_launch": dom_bytes, "issue_slots": issue,
                      "note": ("fused pass 2 + pass 3: the algorithmic bytes count both passes (16 B/cell); the "
                               "z pass reads the y pass's output from L2, so `traffic` (DRAM) is lower")
