@@ -124,7 +124,6 @@ class SlabEngine(object):
                     want //= 2
             if not self.nchunks:
                 mode = "nccl"
-        self._p2lag = max(1, int(os.environ.get("RF_P2LAG", "2")))
         self._xa, self._subs = (split_plan(nx // self.world, self.world, align=pass3_row_align(ny, nz))
                                 if mode == "chunked" else (nx // self.world, []))
         self.mode = mode
@@ -166,10 +165,6 @@ class SlabEngine(object):
                         with torch.cuda.stream(q):
                             dist.all_reduce(self._fence, group=self.group)
 
-                    # pass 2 trails pass 1 by `lag` chunks: the pass-2 launches left over after the last
-                    # pass 1 then cover the transfer of the last chunk (lag 1 leaves the SMs idle for
-                    # most of it: 4 GPUs 6.56 -> see DESIGN.md section 6)
-                    lag = self._p2lag
                     eng.chunk_begin_step()
                     fence()      # peers have finished reading their receive buffers (previous step)
                     for c in range(nc):
@@ -177,10 +172,9 @@ class SlabEngine(object):
                         eng.chunk_exchange_x(c, 0, xa, True)
                         fence()  # every rank's copies of chunk c have landed
                         eng.chunk_arrived(c)
-                        if c >= lag:
-                            eng.chunk_pass2_x(c - lag, 0, xa, c - lag)
-                    for c in range(max(0, nc - lag), nc):
-                        eng.chunk_pass2_x(c, 0, xa, c)
+                        if c >= 1:
+                            eng.chunk_pass2_x(c - 1, 0, xa, c - 1)
+                    eng.chunk_pass2_x(nc - 1, 0, xa, nc - 1)
                     for s, (x0, x1) in enumerate(subs):
                         eng.chunk_exchange_x(-1, x0, x1, False)
                         fence()
