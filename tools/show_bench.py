@@ -8,5 +8,6 @@ for f in sys.argv[1:]:
         print(f, "unreadable:", e)
         continue
     print("%s: n=%d %.3f ms/step %.0f %s | %s | %s" % (
-        f, d["n_gpus"], d["ms_per_step"], d["value"], d["unit"],
-        {k: round(v, 3) for k, v in d["kernels_ms"].items()}, d["config"]["parallelism"][:48]))
+        f, d.get("n_gpus", 1), d["ms_per_step"], d["value"], d["unit"],
+        {k: round(v, 3) for k, v in d.get("kernels_ms", {}).items()} or d.get("impl", ""),
+        str(d.get("config", {}).get("parallelism", ""))[:48]))
