@@ -133,6 +133,24 @@ int rf_stage_symmetrize(int nx, int ny, int nz, int packed, int dtype, void* hos
 int rf_stage_density(long long nelem, int nz, int dtype, int lognormal, double sigma,
                      const double* growth, const double* rho, void* host_real);
 
+/* The same epilogue on DEVICE arrays, for callers that cannot allocate (CUDA graph capture,
+ * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * dev_delta (in) and dev_out (out; may be the same array)
+ * are caller-owned device arrays of nelem reals, last axis nz; growth / rho are host tables of
+ * nz doubles (copied on the stream before the kernels; reusable when the call returns);
+ * sigma <= 0 with lognormal != 0 measures np.std(delta) on the device.  The call enqueues
+ * two copies and two or three kernels on cuda_stream and returns without synchronising; it
+ * calls no cudaMalloc / cudaFree and needs no rf_ctx.  Its scratch (two tables of
+ * RF_NOALLOC_MAX_NZ doubles + 1024 partial sums, 80 KB) is a file-scope __device__ array that
+ * every GPU loading the library holds until exit: nz > RF_NOALLOC_MAX_NZ is rejected with
+ * RF_ERR_ARG.  Every call on a device shares that array and it keeps the last call's contents
+ * (each call overwrites all it reads, so nothing needs clearing): calls that overlap on one
+ * GPU -- different streams, or host threads without ordering -- race; serialise them. */
+#define RF_NOALLOC_MAX_NZ 4096
+int rf_density_noalloc(const void* dev_delta, void* dev_out, long long nelem, int nz, int dtype,
+                       int lognormal, double sigma, const double* growth, const double* rho,
+                       void* cuda_stream);
+
 /* page-locked host memory for result arrays (transform.allocate, transform.py:10-43, uses
  * SIMD-aligned memory for the same reason: fast transfers into the transform) */
 void* rf_host_alloc(long long bytes);

@@ -49,6 +49,7 @@ SIGNATURES = {
     "rf_stage_randomize": (_c.c_int, [_c.c_longlong, _c.c_int, _c.c_uint64, _P]),
     "rf_stage_symmetrize": (_c.c_int, [_c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int, _P]),
     "rf_stage_density": (_c.c_int, [_c.c_longlong, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _P, _P, _P]),
+    "rf_density_noalloc": (_c.c_int, [_P, _P, _c.c_longlong, _c.c_int, _c.c_int, _c.c_int, _c.c_double, _P, _P, _P]),
     "rf_host_alloc": (_P, [_c.c_longlong]),
     "rf_host_free": (None, [_P]),
     "rf_set_timing": (_c.c_int, [_P, _c.c_int]),

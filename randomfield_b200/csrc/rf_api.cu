@@ -2165,3 +2165,132 @@ extern "C" int rf_stage_density(long long nelem, int nz, int dtype, int lognorma
                            : stage_density_impl<double>(nelem, nz, lognormal, sigma, growth, rho, d);
   });
 }
+
+// ------------------------------------------------------------------------------------------
+// rf_density_noalloc: the density epilogue on caller-owned DEVICE arrays without any allocation
+// (for callers that cannot call cudaMalloc: stream capture, serving loops).  No counterpart in
+// the reference.  Same arithmetic as
+// rf_stage_density / stage_density_impl above; the per-z tables and the partial sums of the
+// sigma measurement live in ONE file-scope device array that every call on a device shares.
+// ------------------------------------------------------------------------------------------
+struct NoAllocScratch {
+  double a[RF_NOALLOC_MAX_NZ];      // in: growth[z]    -> out: table a[z] (as double)
+  double b[RF_NOALLOC_MAX_NZ];      // in: rho_mean[z]  -> out: table b[z]
+  double parts[2 * 1024];           // per-CTA (sum, sumsq) of the sigma measurement
+  double sums[2];                   // their fixed-order total
+};
+// Host code must never use this name as a pointer: it is a host-side stand-in for the symbol.
+// noalloc_scratch() below asks the runtime for the device address, once per device.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
+
+static const int kNoAllocMaxDevices = 64;
+static NoAllocScratch* g_noalloc_ptr[kNoAllocMaxDevices];   // device address on each device, 0 = not asked yet
+
+static int noalloc_scratch(NoAllocScratch** out) {
+  int dev = -1;
+  RF_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return fail(RF_ERR_ARG, "rf_density_noalloc: device ordinal out of range");
+  NoAllocScratch* p = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    void* sym = nullptr;
+    RF_CUDA(cudaGetSymbolAddress(&sym, g_noalloc_scratch));   // with `dev` current: this device's copy
+    if (!sym) return fail(RF_ERR_CUDA, "rf_density_noalloc: cudaGetSymbolAddress returned a null address");
+    p = (NoAllocScratch*)sym;
+    __atomic_store_n(&g_noalloc_ptr[dev], p, __ATOMIC_RELEASE);   // same value from every thread
+  }
+  *out = p;
+  return RF_OK;
+}
+
+// one CTA of 256 threads: the total of the partial sums in stats_final_kernel's order (when sigma
+// is to be measured), then growth / rho_mean -> the tables a, b of density_kernel, in place.
+// Every scratch slot read here was written earlier in the same call: nothing has to start at zero.
+template <typename T>
+__global__ void noalloc_tables_kernel(NoAllocScratch* s, int nz, long long nelem, int lognormal, double sigma) {
+  __shared__ double r1[256], r2[256];
+  __shared__ double sig;
+  if (lognormal && !(sigma > 0)) {
+    double s1 = 0, s2 = 0;
+    for (int i = threadIdx.x; i < 1024; i += 256) {
+      s1 += s->parts[2 * i];
+      s2 += s->parts[2 * i + 1];
+    }
+    r1[threadIdx.x] = s1;
+    r2[threadIdx.x] = s2;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if (threadIdx.x < o) {
+        r1[threadIdx.x] += r1[threadIdx.x + o];
+        r2[threadIdx.x] += r2[threadIdx.x + o];
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      s->sums[0] = r1[0];
+      s->sums[1] = r2[0];
+      const double mean = r1[0] / (double)nelem;
+      sig = sqrt(fmax(0.0, r2[0] / (double)nelem - mean * mean));
+    }
+  } else if (threadIdx.x == 0) {
+    sig = sigma;
+  }
+  __syncthreads();
+  for (int z = threadIdx.x; z < nz; z += 256) {
+    const double g = s->a[z], rm = s->b[z];
+    if (lognormal) {
+      const double t = 1.0 + (sig * g) * (sig * g);
+      s->a[z] = (double)(T)(sqrt(log(t)) / sig);
+      s->b[z] = (double)(T)(rm / sqrt(t));
+    } else {
+      s->a[z] = (double)(T)g;
+      s->b[z] = (double)(T)rm;
+    }
+  }
+}
+
+// density_kernel with separate input / output arrays (they may be the same) and double tables
+template <typename T>
+__global__ void noalloc_density_kernel(const T* in, T* out, long long n, int nz,
+                                       const NoAllocScratch* __restrict__ s, int lognormal) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int z = (int)(i % nz);
+    const T d = in[i];
+    const T az = (T)s->a[z], bz = (T)s->b[z];
+    out[i] = lognormal ? exp(d * az) * bz : ((T)1 + az * d) * bz;
+  }
+}
+
+template <typename T>
+static int density_noalloc_impl(NoAllocScratch* s, const void* in, void* out, long long nelem, int nz,
+                                int lognormal, double sigma, cudaStream_t st) {
+  if (lognormal && !(sigma > 0)) {
+    stats_partial_kernel<T><<<1024, 256, 0, st>>>((const T*)in, nelem, s->parts);   // writes all 1024 slots
+    RF_CUDA(cudaGetLastError());
+  }
+  noalloc_tables_kernel<T><<<1, 256, 0, st>>>(s, nz, nelem, lognormal, sigma);
+  RF_CUDA(cudaGetLastError());
+  noalloc_density_kernel<T><<<grid_for(nelem), 256, 0, st>>>((const T*)in, (T*)out, nelem, nz, s, lognormal);
+  RF_CUDA(cudaGetLastError());
+  return RF_OK;
+}
+
+extern "C" int rf_density_noalloc(const void* dev_delta, void* dev_out, long long nelem, int nz, int dtype,
+                                  int lognormal, double sigma, const double* growth, const double* rho,
+                                  void* cuda_stream) {
+  if (!dev_delta || !dev_out || !growth || !rho || nz <= 0 || nelem <= 0 || nelem % nz)
+    return fail(RF_ERR_ARG, "rf_density_noalloc: bad argument");
+  if (dtype != RF_F32 && dtype != RF_F64) return fail(RF_ERR_ARG, "rf_density_noalloc: dtype must be RF_F32 or RF_F64");
+  if (nz > RF_NOALLOC_MAX_NZ)
+    return fail(RF_ERR_ARG, "rf_density_noalloc: nz = " + std::to_string(nz) + " exceeds RF_NOALLOC_MAX_NZ = " +
+                                std::to_string(RF_NOALLOC_MAX_NZ) + " (the static scratch holds two tables of that length)");
+  NoAllocScratch* s = nullptr;
+  int e = noalloc_scratch(&s);
+  if (e) return e;
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  // the tables start as growth / rho_mean; the copies are ordered on `st` before the kernels
+  RF_CUDA(cudaMemcpyAsync(s->a, growth, sizeof(double) * nz, cudaMemcpyHostToDevice, st));
+  RF_CUDA(cudaMemcpyAsync(s->b, rho, sizeof(double) * nz, cudaMemcpyHostToDevice, st));
+  return dtype == RF_F32 ? density_noalloc_impl<float>(s, dev_delta, dev_out, nelem, nz, lognormal, sigma, st)
+                         : density_noalloc_impl<double>(s, dev_delta, dev_out, nelem, nz, lognormal, sigma, st);
+}
