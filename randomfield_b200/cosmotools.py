@@ -51,6 +51,7 @@ class LiteFlatLambdaCDM(object):
         self.has_massive_nu = self.Tcmb0 > 0 and any(m > 0 for m in self.m_nu)
         self.Onu0 = self.Ogamma0 * self._nu_relative_density(0.) if self.Tcmb0 > 0 else 0.
         self.Ode0 = 1. - self.Om0 - self.Ogamma0 - self.Onu0
+        self.Odm0 = None if self.Ob0 is None else self.Om0 - self.Ob0
 
     def _nu_relative_density(self, z):
         z = np.asarray(z, dtype=float)
@@ -117,6 +118,67 @@ def create_cosmology(*args, **kwargs):
     kwargs.setdefault('Tcmb0', 0.)
     kwargs.setdefault('m_nu', (0., 0., 0.))
     return LiteFlatLambdaCDM(**kwargs)
+
+
+def get_class_parameters(cosmology):
+    """CLASS parameter dictionary of a background model (cosmotools.py:48-97).  Works on astropy
+    FLRW objects and on LiteFlatLambdaCDM; raises ValueError when an attribute is missing."""
+    out = {}
+    try:
+        out['h'] = cosmology.h
+        out['T_cmb'] = _value(cosmology.Tcmb0)
+        out['Omega_b'] = cosmology.Ob0
+        out['Omega_cdm'] = cosmology.Odm0 - cosmology.Onu0      # cold = dark - massive neutrinos
+        out['Omega_k'] = cosmology.Ok0
+        out['Omega_scf'] = 0.                                    # CLASS fills in the component left out
+        if hasattr(cosmology, 'w0'):
+            out.update(w0_fld=cosmology.w0, wa_fld=0., Omega_Lambda=0.)
+        else:
+            out['Omega_fld'] = 0.
+        n_massive = 0
+        if cosmology.has_massive_nu:
+            masses = cosmology.m_nu
+            if np.ndim(_value(masses)) == 0:
+                n_massive, masses = 3, [3 * masses]              # one value = three degenerate species
+            else:
+                n_massive = len(masses)
+            if n_massive > 3:
+                raise RuntimeError('Cannot calculate cosmology with >3 massive neutrinos.')
+            heavy = [repr(float(_value(m))) for m in masses if _value(m) > 0]
+            n_massive -= len(masses) - len(heavy)
+            if n_massive > 0:
+                out['m_ncdm'] = ','.join(heavy)
+        out['N_ncdm'] = n_massive
+        out['N_ur'] = 3.00641 - n_massive + (3 - n_massive) * (cosmology.Neff - 3.00641) / 3.
+    except AttributeError:
+        raise ValueError('Cosmology is missing required attributes.')
+    return out
+
+
+def calculate_power(cosmology, k_min, k_max, z=0, num_k=500, scaled_by_h=True,
+                    n_s=0.9619, logA=3.0980):
+    """P(k, z) on num_k log-spaced points of [k_min, k_max] from CLASS (cosmotools.py:100-137).
+    Host-side set-up, outside the device path; without the `classy` package it raises the
+    reference's RuntimeError, which is what Generator(cosmology=..., power=None) reports."""
+    try:
+        from classy import Class
+        engine = Class()
+    except ImportError:
+        raise RuntimeError('power.calculate_power requires classy.')
+    pars = get_class_parameters(cosmology)
+    pars['output'] = 'mPk'
+    pars['P_k_max_h/Mpc' if scaled_by_h else 'P_k_max_1/Mpc'] = k_max
+    pars['n_s'] = n_s
+    pars['ln10^{10}A_s'] = logA
+    engine.set(pars)
+    engine.compute()
+    h = engine.h() if scaled_by_h else 1.
+    table = np.empty((num_k,), dtype=[('k', float), ('Pk', float)])
+    table['k'][:] = np.logspace(np.log10(k_min), np.log10(k_max), num_k)
+    table['Pk'][:] = [engine.pk(k * h, z) * h ** 3 for k in table['k']]
+    engine.struct_cleanup()
+    engine.empty()
+    return table
 
 
 def _value(q, unit=None):

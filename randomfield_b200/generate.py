@@ -187,7 +187,8 @@ class Generator(object):
         else:
             self.cosmology = cosmology
             if power is None:
-                raise RuntimeError('power.calculate_power requires classy.')
+                power = cosmotools.calculate_power(self.cosmology, k_min=self.k_min, k_max=self.k_max,
+                                                   scaled_by_h=True)
         self.power = powertools.validate_power(power)
 
         probe = np.empty((1, 1, nz), dtype=self._real_dtype)

@@ -97,3 +97,35 @@ def test_generator_tables_are_consistent():
     assert np.all(np.diff(rho) > 0)
     dc = cosmotools._value(model.comoving_distance(z)) * model.h
     assert np.allclose(dc, np.arange(nz) * spacing, atol=2e-3 * spacing)
+
+
+def test_class_parameters_of_the_default_model():
+    """cosmotools.get_class_parameters (cosmotools.py:48-97) on the Planck13 stand-in: one massive
+    species of 0.06 eV, the other two light; a missing attribute is a ValueError."""
+    c = create_cosmology()
+    if not isinstance(c, cosmotools.LiteFlatLambdaCDM):
+        pytest.skip("astropy model in use")
+    p = cosmotools.get_class_parameters(c)
+    assert p['h'] == pytest.approx(0.6777) and p['T_cmb'] == pytest.approx(2.7255)
+    assert p['Omega_b'] == pytest.approx(0.048252)
+    assert p['Omega_cdm'] == pytest.approx(0.30712 - 0.048252 - c.Onu0)
+    assert p['Omega_k'] == 0. and p['Omega_scf'] == 0. and p['Omega_fld'] == 0.
+    assert 'w0_fld' not in p
+    assert p['N_ncdm'] == 1 and p['m_ncdm'] == '0.06'
+    assert p['N_ur'] == pytest.approx(3.00641 - 1 + 2 * (3.046 - 3.00641) / 3.)
+    # massless neutrinos: no m_ncdm entry, three light species
+    q = cosmotools.get_class_parameters(cosmotools.LiteFlatLambdaCDM(H0=70., Om0=0.3, Ob0=0.05, m_nu=(0., 0., 0.)))
+    assert q['N_ncdm'] == 0 and 'm_ncdm' not in q and q['N_ur'] == pytest.approx(3.046)
+    with pytest.raises(ValueError):
+        cosmotools.get_class_parameters(object())
+
+
+def test_calculate_power_without_class_raises_the_reference_error():
+    """cosmotools.py:105-109: no classy -> RuntimeError('power.calculate_power requires classy.')."""
+    try:
+        import classy  # noqa: F401
+        pytest.skip("classy is installed")
+    except ImportError:
+        pass
+    with pytest.raises(RuntimeError, match='requires classy'):
+        cosmotools.calculate_power(create_cosmology(), 1e-3, 1.0)
