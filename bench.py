@@ -6,8 +6,8 @@
 A step is one full pass of the hot path (generate + 3 FFT passes) for a new seed.
 Workloads (weak scaling, 1024^3 cells per GPU):
   N=1: 1024^3 (the single-GPU configuration BASELINE.json's metric is quoted on)
-  N=2: 2048x2048x512 (BASELINE config 4)   N=4: 2048x2048x1024   N=8: 2048^3
-  --grid 4096,4096,4096 --gpus 8 runs the 4096^3 configuration of the metric.
+  N=2: 2048x2048x512 (BASELINE config 4)   N=4: 2048x2048x1024
+  N=8: 4096^3 (the 8-GPU configuration of the metric; 8 x 2^33 cells)
 `value`  : device-timed, nothing crosses PCIe, field left resident in HBM.
 `e2e`    : the same metric through Generator.generate_delta_field() returning a host numpy
            array (table upload + device->host copy of the field inside the timed region).
@@ -201,6 +201,17 @@ def exchange_mode(world):
     return mode
 
 
+def split_note(grid, world):
+    """The split schedule SlabEngine would pick for this grid (slab.split_plan reads the same
+    environment; default on from 8 ranks), as a suffix of the parallelism string."""
+    from randomfield_b200 import slab
+    nxl = grid[0] // world
+    xa, subs = slab.split_plan(nxl, world, align=slab.pass3_row_align(grid[1], grid[2]))
+    if not subs:
+        return ""
+    return "; rows [0, %d) of each x-slab travel with pass 1, the rest in %d x ranges under passes 2 + 3" % (xa, len(subs))
+
+
 def workload_config(grid, world, mode=None):
     """`config` of the JSON line: identical in the GPU arm and in the reference arm."""
     mode = mode or exchange_mode(world)
@@ -208,7 +219,7 @@ def workload_config(grid, world, mode=None):
     par = "single GPU" if world == 1 else "y-slab k-space -> %s -> x-slab real space" % {
         "direct": "pass-1 stores into peer receive buffers over NVLink (no separate all-to-all)",
         "chunked": "copy-engine pushes into peer receive buffers, pipelined with passes 1 and 2 over chunks "
-                   "of z columns",
+                   "of z columns" + split_note(grid, world),
         "nccl": "NCCL all-to-all"}.get(mode, mode)
     return {"workload": workload_name(grid, world), "grid": list(grid),
             "l2": ("working set %.1f GB per GPU >> 126 MB L2, no flush needed" % (4 * local / 1e9)) if 4 * local > 1e9

@@ -47,14 +47,15 @@ def split_plan(nxl, world, frac=None, nsub=None, align=1):
     the local x-slab cross NVLink while pass 1 runs, the rest afterwards in `nsub` ranges whose
     pass 2 + pass 3 overlap the next range's transfer.  Returns (xa, [(x0, x1), ...]);
     no ranges = the plain chunked schedule.  Range edges are multiples of `align` rows (pass 3
-    works on whole 64 KB tiles of lines).  Opt-in (RF_SPLIT_A = fraction of rows sent with pass 1,
-    RF_SPLIT_NSUB = later ranges): measured on B200 x4 / x8 the step is bound by the kernels and
-    by the copy engines' share of HBM at about the same level, so hiding pass 3 behind the tail
-    of the transfer gains 1 % at 8 ranks and loses 1 % at 4."""
+    works on whole 64 KB tiles of lines).  RF_SPLIT_A = fraction of rows sent with pass 1,
+    RF_SPLIT_NSUB = later ranges.  Default: on for 8 ranks and more (0.7, 2), off below.  Measured
+    on B200: 4096^3 on 8 GPUs 57.3 ms plain, 53.6 / 55.1 / 53.6 ms with
+    (0.6, 2) / (0.7, 2) / (0.8, 2), 56.5 ms with (0.45, 4) -- pass 3 of the early rows hides behind the
+    tail of the transfer; on 4 GPUs the kernels bound the step and the split loses 1 %."""
     if frac is None:
-        frac = float(os.environ.get("RF_SPLIT_A", "1"))
+        frac = float(os.environ.get("RF_SPLIT_A", "0.7" if world >= 8 else "1"))
     if nsub is None:
-        nsub = int(os.environ.get("RF_SPLIT_NSUB", "4"))
+        nsub = int(os.environ.get("RF_SPLIT_NSUB", "2" if world >= 8 else "4"))
     units = nxl // align if align > 0 and nxl % align == 0 else 0
     if not 0.0 < frac < 1.0 or nsub < 1 or units < 2:
         return nxl, []
