@@ -184,6 +184,24 @@ def test_split_plan_covers_the_slab():
                     assert all(e % align == 0 for e in edges) or not subs
 
 
+def test_split_plan_defaults(monkeypatch):
+    """Without RF_SPLIT_A / RF_SPLIT_NSUB: plain chunked schedule below 8 ranks, (0.7, 2) from 8 ranks
+    (4096^3 on 8 GPUs: rows [0, 358) with pass 1, then two ranges); the environment overrides both."""
+    from randomfield_b200 import slab
+    monkeypatch.delenv("RF_SPLIT_A", raising=False)
+    monkeypatch.delenv("RF_SPLIT_NSUB", raising=False)
+    for world in (2, 4):
+        assert slab.split_plan(2048 // world, world) == (2048 // world, [])
+    xa, subs = slab.split_plan(512, 8, align=slab.pass3_row_align(4096, 4096))
+    assert xa == 358 and subs == [(358, 435), (435, 512)]
+    monkeypatch.setenv("RF_SPLIT_A", "1")
+    assert slab.split_plan(512, 8) == (512, [])
+    monkeypatch.setenv("RF_SPLIT_A", "0.5")
+    monkeypatch.setenv("RF_SPLIT_NSUB", "4")
+    xa, subs = slab.split_plan(512, 4)
+    assert xa == 256 and len(subs) == 4 and subs[-1][1] == 512
+
+
 def test_pass3_row_align():
     from randomfield_b200 import slab
     # 64 KB pass-3 tiles: nz = 64 -> 256 lines per tile, ny = 64 lines per x row -> 4 rows per tile
